@@ -1,0 +1,109 @@
+// Shared helpers for the libavtubes kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/avtubes.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libavtubes targets sm_100a (B200) only"
+#endif
+
+namespace avt {
+
+void set_error(const char* fmt, ...);
+
+#define AVT_CHECK_CUDA(expr)                                                        \
+    do {                                                                            \
+        cudaError_t _e = (expr);                                                    \
+        if (_e != cudaSuccess) {                                                    \
+            avt::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),  \
+                           __FILE__, __LINE__);                                     \
+            return AVT_ERR_CUDA;                                                    \
+        }                                                                           \
+    } while (0)
+
+#define AVT_REQUIRE(cond, ...)                                                      \
+    do {                                                                            \
+        if (!(cond)) {                                                              \
+            avt::set_error(__VA_ARGS__);                                            \
+            return AVT_ERR_INVALID;                                                 \
+        }                                                                           \
+    } while (0)
+
+#define AVT_LAUNCH_CHECK()                                                          \
+    do {                                                                            \
+        cudaError_t _e = cudaGetLastError();                                        \
+        if (_e != cudaSuccess) {                                                    \
+            avt::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), \
+                           __FILE__, __LINE__);                                     \
+            return AVT_ERR_CUDA;                                                    \
+        }                                                                           \
+    } while (0)
+
+constexpr float kNormEps = 1e-12f;          // torch.nn.functional.normalize default eps
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct HeadParams {
+    float eps, eps2, tau, temp, mask_scale;
+    int trimap, use_neg;
+};
+
+__device__ __forceinline__ float warp_sum(float x) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    return x;
+}
+__device__ __forceinline__ float warp_max(float x) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+    return x;
+}
+__device__ __forceinline__ int warp_sum_i(int x) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    return x;
+}
+
+// sigma((s - eps)/tau) with RELATIVE accuracy for tiny values (they are weights of a
+// ratio): 1 / (1 + 2^(-z*log2e)), ex2.approx + rcp.approx.
+__device__ __forceinline__ float fast_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+// accurate variant for the fp32 path (expf-based, keeps relative accuracy too)
+__device__ __forceinline__ float sigmoid_acc(float z) {
+    return 1.0f / (1.0f + expf(-z));
+}
+
+// layout of the small per-call scratch at the head of every head workspace
+struct HeadScratch {
+    unsigned int rows_done;      // last-block-done counter of the row-finish kernel
+    unsigned int pad[63];
+};
+
+// ---- kernel launchers implemented in the .cu files -------------------------------
+// prep: rnorm_v, A (positive map), msum (mean_c v_hat), optional bf16 K-major copy
+int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_idx, int col_offset,
+                       int N_v, int N_a, int C, int P, float* rnorm_v, float* A, float* msum,
+                       __nv_bfloat16* vt_bf16, HeadScratch* scratch, cudaStream_t st);
+int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int P, HeadParams hp,
+                       float* Pos, float* Neg, float* weighted_A, float* logits,
+                       float* loss_rows, float* loss_sum, HeadScratch* scratch, cudaStream_t st);
+int launch_sim_fp32(const float* v, const float* a_hat, const float* rnorm_v,
+                    const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
+                    HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
+int launch_sim_bf16(const __nv_bfloat16* vt_bf16, const __nv_bfloat16* a_bf16, const float* rnorm_v,
+                    const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
+                    HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
+int launch_audio_to_bf16(const float* a_hat, int N_a, int N_a_pad, int C, __nv_bfloat16* out,
+                         cudaStream_t st);
+
+}  // namespace avt

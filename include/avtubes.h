@@ -1,0 +1,146 @@
+/*
+ * avtubes.h -- C ABI of libavtubes.so (sm_100a CUDA kernels for the audio-visual
+ * similarity + hard-way localisation head and the cIoU/AUC evaluation).
+ *
+ * The reference (tonymisic/audio-visual-tubes) has no FFI: the path sits behind
+ * Python call signatures.  Each entry point below names the
+ * reference lines it replaces.  All pointers are DEVICE pointers unless the name
+ * ends in _host; all tensors are caller-owned, contiguous and 16-byte aligned.
+ * Every call only enqueues work on `stream` (a cudaStream_t passed as void*);
+ * no call synchronises the device, allocates persistent memory, throws or exits.
+ *
+ * Return value: 0 = ok, negative = error (avt_last_error() gives the text, per thread).
+ *
+ * Layouts
+ *   v        [N_v, C, P]  fp32   raw visual maps, NCHW with H*W flattened (P = 196)
+ *   a / a_hat[N_a, C]     fp32   pooled audio embeddings, raw / L2-normalised
+ *   pos_idx  [N_v]        int32  column of a_hat that is row n's positive, or NULL
+ *                                for pos[n] = col_offset + n (model.py:115 has
+ *                                pos = arange(B); col_offset serves row-sharded ranks)
+ *   logits   [N_v, L]     fp32   L = N_a + 1 + use_neg  (model.py:143-146)
+ */
+#ifndef AVTUBES_H_
+#define AVTUBES_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AVT_OK                 0
+#define AVT_ERR_INVALID       -1   /* bad shape / null pointer / unsupported size   */
+#define AVT_ERR_CUDA          -2   /* a CUDA runtime or driver call failed          */
+#define AVT_ERR_WORKSPACE     -3   /* workspace too small (see *_workspace_bytes)   */
+#define AVT_ERR_UNSUPPORTED   -4   /* device is not sm_100 / feature not built      */
+
+/* precision of the all-pairs contraction (model.py:125) */
+#define AVT_PRECISION_FP32     0   /* CUDA-core fp32 FMA, the reference's own arithmetic */
+#define AVT_PRECISION_BF16     1   /* tcgen05 kind::f16 (bf16 operands, fp32 accumulate in TMEM) */
+
+/* ground-truth rasterisation modes (utils.py:241-309) */
+#define AVT_GT_VGGSS           0   /* union of boxes            -> weights {0,1},   den 1 */
+#define AVT_GT_FLICKR          1   /* sum of annotators, clip 2 -> weights {0,1,2}, den 2 */
+#define AVT_GT_FLICKR_FRAME    2   /* raw sum of boxes          -> counts,          den 1 */
+
+int         avt_version(void);
+const char* avt_last_error(void);
+/* 1 if the current device can run the library (compute capability 10.x), else 0 */
+int         avt_device_ok(void);
+
+/* ---- audio embedding normalisation ---------------------------------------------
+ * F.normalize(aud, dim=1)                        model.py:122 (tube :31)
+ * a_hat[k,:] = a[k,:] / max(||a[k,:]||, 1e-12);  rnorm_a[k] = 1 / max(||a[k,:]||, 1e-12) */
+int avt_audio_normalize(const float* a, int N_a, int C,
+                        float* a_hat, float* rnorm_a, void* stream);
+/* adjoint: da[k,:] = rnorm_a[k] * (d_ahat[k,:] - a_hat[k,:] * <a_hat[k,:], d_ahat[k,:]>) */
+int avt_audio_normalize_backward(const float* a_hat, const float* rnorm_a,
+                                 const float* d_ahat, int N_a, int C,
+                                 float* da, void* stream);
+
+/* ---- similarity + hard-way loss head --------------------------------------------
+ * Replaces model.py:117 (F.normalize(img)), :124-125 (both einsums), :128-135
+ * (tri-map sigmoids), :138-146 (masked pooling, diagonal mask, logits), :148-152
+ * (weighted_A) and nn.CrossEntropyLoss(logits, 0) (train_hardway_1frame.py:113,131);
+ * tube model: model.py:35,47-59.  The N_v x N_a x P similarity tensor is never
+ * written to memory.
+ *
+ * Outputs
+ *   A, Pos, Neg  [N_v, P]        model.py:124,128,131/133  (returned maps)
+ *   logits       [N_v, L]
+ *   loss_rows    [N_v]           logsumexp(logits[n]) - logits[n,0]
+ *   loss_sum     [1] or NULL     sum_n loss_rows[n] (deterministic order)
+ *   weighted_A   [N_v, P] or NULL model.py:148-152
+ * Saved for backward (all required)
+ *   rnorm_v [N_v, P], sim [N_v, N_a] (pooled, before mask), den [N_v, N_a] */
+size_t avt_head_workspace_bytes(int N_v, int N_a, int C, int P, int precision, int backward);
+
+int avt_head_forward(const float* v, const float* a_hat,
+                     int N_v, int N_a, int C, int P,
+                     const int32_t* pos_idx, int col_offset,
+                     float eps, float eps2, float tau, float temp, float mask_scale,
+                     int trimap, int use_neg, int precision,
+                     float* A, float* Pos, float* Neg, float* logits,
+                     float* loss_rows, float* loss_sum, float* weighted_A,
+                     float* rnorm_v, float* sim, float* den,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* Backward of the head (autograd of model.py:117-146 + CrossEntropyLoss).
+ * Gradient of   dloss_scale * sum_n loss_rows[n]  +  <dlogits, logits>  +  <dA, A>
+ * (dlogits, dA may be NULL).  Writes dv [N_v, C, P] (gradient wrt the RAW maps) and
+ * d_ahat [N_a, C] (gradient wrt the NORMALISED audio rows, summed over this call's
+ * N_v rows; finish with avt_audio_normalize_backward, after a reduce-scatter when
+ * rows are sharded over ranks). */
+int avt_head_backward(const float* v, const float* a_hat,
+                      int N_v, int N_a, int C, int P,
+                      const int32_t* pos_idx, int col_offset,
+                      float eps, float eps2, float tau, float temp, float mask_scale,
+                      int trimap, int use_neg, int precision,
+                      const float* A, const float* logits, const float* loss_rows,
+                      const float* rnorm_v, const float* sim, const float* den,
+                      float dloss_scale, const float* dlogits, const float* dA,
+                      float* dv, float* d_ahat,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- evaluation -------------------------------------------------------------------
+ * One launch for the reference's per-clip glue, train_hardway_1frame.py:198-207
+ * (== test.py:97-107): cv2.resize 14->224 INTER_LINEAR, utils.normalize_img(-h)
+ * (utils.py:234-239), pred = 1 - h, threshold = sorted(pred)[25088], binarise with a
+ * strict '>', Evaluator.cal_CIOU(pred, gt, 0.5) (utils.py:209-214).
+ *
+ *   maps14     [N, 14, 14] fp32
+ *   gt_dense   [N, 224, 224] uint8 weights (gt = weight / gt_den), or NULL to rasterise
+ *   boxes      [N, max_boxes, 4] int16 pixel rectangles (xmin, ymin, xmax, ymax) as
+ *              utils.py:254,267 derive them, box_count [N] uint8; used when gt_dense NULL
+ *   gt_mode    AVT_GT_*           (fixes gt_den: 1, 2, 1)
+ *   up224      [N, 224, 224] fp32 or NULL     the upsampled map (train_hardway_1frame.py:198)
+ *   mask       [N, 224, 224] uint8 or NULL    the binary prediction (:203-204)
+ *   inter_w, union_w [N] int32    integer numerator / denominator in weight units:
+ *              ciou = inter_w / union_w exactly as utils.py:212-214 computes in float64
+ *   ciou       [N] float64        (NaN when union_w == 0, as numpy)            */
+int avt_eval_maps(const float* maps14, int N,
+                  const uint8_t* gt_dense,
+                  const int16_t* boxes, const uint8_t* box_count, int max_boxes, int gt_mode,
+                  float* up224, uint8_t* mask,
+                  int32_t* inter_w, int32_t* union_w, double* ciou, void* stream);
+
+/* utils.py:241-274 / 276-309: boxes -> dense weight map [N,224,224] uint8 */
+int avt_rasterise_gt(const int16_t* boxes, const uint8_t* box_count, int N, int max_boxes,
+                     int gt_mode, uint8_t* gt_dense, void* stream);
+
+/* train_hardway_1frame.py:208-215 / utils.py:216-229:
+ *   counts[i] = #{ciou >= 0.05*i}, i = 0..20 (float64 compare, NaN never counts);
+ *   out[0] = cIoU@0.5 = counts-style mean(ciou >= 0.5); out[1] = trapezoid AUC.
+ * counts [21] int32, out [2] float64 (device). */
+int avt_auc(const double* ciou, int N, int32_t* counts, double* out, void* stream);
+
+/* utils.py:311-318 mTC: mean over consecutive frames of cal_CIOU(mask[i], mask[i+1], 0.5).
+ * masks [T,224,224] uint8 {0,1}; pair_inter, pair_union [T-1] int32; out [1] float32. */
+int avt_mtc(const uint8_t* masks, int T, int32_t* pair_inter, int32_t* pair_union,
+            float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AVTUBES_H_ */
