@@ -100,9 +100,26 @@ int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int 
 int launch_sim_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
-int launch_sim_bf16(const __nv_bfloat16* vt_bf16, const __nv_bfloat16* a_bf16, const float* rnorm_v,
+int launch_row_grad(const float* A, const float* logits, const float* loss_rows,
+                    const int32_t* pos_idx, int col_offset, int N_v, int N_a, int P, HeadParams hp,
+                    float dloss_scale, const float* dlogits, const float* dA, float* gsim, float* GA,
+                    cudaStream_t st);
+int launch_bwd_fp32(const float* v, const float* a_hat, const float* rnorm_v,
+                    const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
+                    HeadParams hp, const float* sim, const float* den, const float* gsim,
+                    const float* GA, float* dvh, float* dah, cudaStream_t st);
+int launch_dv_finish(const float* v, const float* rnorm_v, int N_v, int C, int P, float* dv,
+                     cudaStream_t st);
+// tcgen05 path (avt_head_tc.cu): vt = normalised maps, bf16 [N_v*P (+slack)][C]; a_bf = audio
+// rows, bf16 [n_a_pad][C] (rows >= N_a zero)
+int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
+int launch_bwd_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, __nv_bfloat16* at_bf,
+                    __nv_bfloat16* g_bf, const float* a_hat, const float* rnorm_v,
+                    const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C,
+                    int P, HeadParams hp, const float* sim, const float* den, const float* gsim,
+                    const float* GA, float* dv, float* d_ahat, cudaStream_t st);
 int launch_audio_to_bf16(const float* a_hat, int N_a, int N_a_pad, int C, __nv_bfloat16* out,
                          cudaStream_t st);
 

@@ -1,0 +1,161 @@
+// C ABI of the similarity + hard-way loss head: argument checks, workspace carving and
+// the launch sequence of both precisions.  Nothing here synchronises or allocates.
+#include "avt_common.cuh"
+
+namespace avt {
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Workspace layout (all offsets 1024-byte aligned).  The forward leaves the bf16 operand
+// copies in place; a backward called with the same workspace reuses them.
+struct HeadWorkspace {
+    size_t scratch, msum, gsim, ga, vt, a_bf, at_bf, g_bf, total;
+};
+
+HeadWorkspace head_workspace_layout(int N_v, int N_a, int C, int P, int precision, int backward) {
+    HeadWorkspace w{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 1024); return o; };
+    w.scratch = take(sizeof(HeadScratch));
+    w.msum = take((size_t)N_v * P * sizeof(float));
+    w.gsim = w.ga = w.vt = w.a_bf = w.at_bf = w.g_bf = 0;
+    if (precision == AVT_PRECISION_BF16) {
+        const size_t n_a_pad = align_up((size_t)N_a, 128);
+        // + one tile of slack rows so the last image's 208-row TMA box stays in bounds
+        w.vt = take(((size_t)N_v * P + 64) * C * sizeof(__nv_bfloat16));
+        w.a_bf = take(n_a_pad * C * sizeof(__nv_bfloat16));
+        if (backward) {
+            w.at_bf = take((size_t)C * n_a_pad * sizeof(__nv_bfloat16));
+            w.g_bf = take(((size_t)N_v * P + 128) * n_a_pad * sizeof(__nv_bfloat16));
+        }
+    }
+    if (backward) {
+        w.gsim = take((size_t)N_v * N_a * sizeof(float));
+        w.ga = take((size_t)N_v * P * sizeof(float));
+    }
+    w.total = off;
+    return w;
+}
+
+static int check_shapes(const char* fn, int N_v, int N_a, int C, int P, int precision) {
+    AVT_REQUIRE(N_v > 0 && N_a > 0, "%s: N_v=%d N_a=%d must be positive", fn, N_v, N_a);
+    AVT_REQUIRE(C > 0 && C % 64 == 0, "%s: C=%d must be a positive multiple of 64", fn, C);
+    AVT_REQUIRE(P > 0 && P <= 256, "%s: P=%d must be in 1..256", fn, P);
+    AVT_REQUIRE(precision == AVT_PRECISION_FP32 || precision == AVT_PRECISION_BF16,
+                "%s: unknown precision %d", fn, precision);
+    if (precision == AVT_PRECISION_BF16) {
+        AVT_REQUIRE(P <= 208 && P % 4 == 0, "%s: bf16 path needs P <= 208 and P %% 4 == 0 (P=%d)", fn, P);
+        AVT_REQUIRE(C % 64 == 0 && C <= 4096, "%s: bf16 path needs C %% 64 == 0", fn);
+    }
+    return AVT_OK;
+}
+
+}  // namespace avt
+
+using namespace avt;
+
+extern "C" size_t avt_head_workspace_bytes(int N_v, int N_a, int C, int P, int precision,
+                                           int backward) {
+    if (N_v <= 0 || N_a <= 0 || C <= 0 || P <= 0) return 0;
+    return head_workspace_layout(N_v, N_a, C, P, precision, backward).total;
+}
+
+extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int N_a, int C, int P,
+                                const int32_t* pos_idx, int col_offset, float eps, float eps2,
+                                float tau, float temp, float mask_scale, int trimap, int use_neg,
+                                int precision, float* A, float* Pos, float* Neg, float* logits,
+                                float* loss_rows, float* loss_sum, float* weighted_A,
+                                float* rnorm_v, float* sim, float* den, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+    int rc = check_shapes("avt_head_forward", N_v, N_a, C, P, precision);
+    if (rc != AVT_OK) return rc;
+    AVT_REQUIRE(v && a_hat && A && Pos && Neg && logits && loss_rows && rnorm_v && sim && den,
+                "avt_head_forward: null pointer among required arguments");
+    AVT_REQUIRE(tau > 0.f && temp > 0.f, "avt_head_forward: tau and temp must be positive");
+    AVT_REQUIRE(workspace != nullptr, "avt_head_forward: workspace is null");
+    // the forward regions lead both layouts, so a workspace sized for backward works too
+    HeadWorkspace w = head_workspace_layout(N_v, N_a, C, P, precision, 0);
+    if (workspace_bytes < w.total) {
+        set_error("avt_head_forward: workspace %zu B < required %zu B", workspace_bytes, w.total);
+        return AVT_ERR_WORKSPACE;
+    }
+    char* ws = static_cast<char*>(workspace);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    HeadParams hp{eps, eps2, tau, temp, mask_scale, trimap, use_neg};
+    HeadScratch* scratch = reinterpret_cast<HeadScratch*>(ws + w.scratch);
+    float* msum = reinterpret_cast<float*>(ws + w.msum);
+
+    if (precision == AVT_PRECISION_FP32) {
+        rc = launch_prep_visual(v, a_hat, pos_idx, col_offset, N_v, N_a, C, P, rnorm_v, A, msum,
+                                nullptr, scratch, st);
+        if (rc != AVT_OK) return rc;
+        rc = launch_sim_fp32(v, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim,
+                             den, st);
+        if (rc != AVT_OK) return rc;
+    } else {
+        if (!avt_device_ok()) {
+            set_error("avt_head_forward: the bf16 tcgen05 path needs an sm_100 device");
+            return AVT_ERR_UNSUPPORTED;
+        }
+        __nv_bfloat16* vt = reinterpret_cast<__nv_bfloat16*>(ws + w.vt);
+        __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
+        const int n_a_pad = (N_a + 127) / 128 * 128;
+        rc = launch_audio_to_bf16(a_hat, N_a, n_a_pad, C, a_bf, st);
+        if (rc != AVT_OK) return rc;
+        rc = launch_prep_visual(v, a_hat, pos_idx, col_offset, N_v, N_a, C, P, rnorm_v, A, msum, vt,
+                                scratch, st);
+        if (rc != AVT_OK) return rc;
+        rc = launch_sim_bf16(vt, a_bf, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den, st);
+        if (rc != AVT_OK) return rc;
+    }
+    return launch_finish_rows(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A, logits, loss_rows,
+                              loss_sum, scratch, st);
+}
+
+extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, int N_a, int C, int P,
+                                 const int32_t* pos_idx, int col_offset, float eps, float eps2,
+                                 float tau, float temp, float mask_scale, int trimap, int use_neg,
+                                 int precision, const float* A, const float* logits,
+                                 const float* loss_rows, const float* rnorm_v, const float* sim,
+                                 const float* den, float dloss_scale, const float* dlogits,
+                                 const float* dA, float* dv, float* d_ahat, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+    int rc = check_shapes("avt_head_backward", N_v, N_a, C, P, precision);
+    if (rc != AVT_OK) return rc;
+    AVT_REQUIRE(v && a_hat && A && logits && loss_rows && rnorm_v && sim && den && dv && d_ahat,
+                "avt_head_backward: null pointer among required arguments");
+    AVT_REQUIRE(workspace != nullptr, "avt_head_backward: workspace is null");
+    HeadWorkspace w = head_workspace_layout(N_v, N_a, C, P, precision, 1);
+    if (workspace_bytes < w.total) {
+        set_error("avt_head_backward: workspace %zu B < required %zu B", workspace_bytes, w.total);
+        return AVT_ERR_WORKSPACE;
+    }
+    char* ws = static_cast<char*>(workspace);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    HeadParams hp{eps, eps2, tau, temp, mask_scale, trimap, use_neg};
+    float* gsim = reinterpret_cast<float*>(ws + w.gsim);
+    float* GA = reinterpret_cast<float*>(ws + w.ga);
+
+    rc = launch_row_grad(A, logits, loss_rows, pos_idx, col_offset, N_v, N_a, P, hp, dloss_scale,
+                         dlogits, dA, gsim, GA, st);
+    if (rc != AVT_OK) return rc;
+    AVT_CHECK_CUDA(cudaMemsetAsync(d_ahat, 0, (size_t)N_a * C * sizeof(float), st));
+    if (precision == AVT_PRECISION_FP32) {
+        AVT_CHECK_CUDA(cudaMemsetAsync(dv, 0, (size_t)N_v * C * P * sizeof(float), st));
+        rc = launch_bwd_fp32(v, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a, C, P, hp, sim, den,
+                             gsim, GA, dv, d_ahat, st);
+        if (rc != AVT_OK) return rc;
+        return launch_dv_finish(v, rnorm_v, N_v, C, P, dv, st);
+    }
+    if (!avt_device_ok()) {
+        set_error("avt_head_backward: the bf16 tcgen05 path needs an sm_100 device");
+        return AVT_ERR_UNSUPPORTED;
+    }
+    const int n_a_pad = (N_a + 127) / 128 * 128;
+    __nv_bfloat16* vt = reinterpret_cast<__nv_bfloat16*>(ws + w.vt);
+    __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
+    __nv_bfloat16* at_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.at_bf);
+    __nv_bfloat16* g_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.g_bf);
+    return launch_bwd_bf16(vt, a_bf, at_bf, g_bf, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
+                           n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, st);
+}

@@ -60,6 +60,7 @@ int launch_audio_to_bf16(const float* a_hat, int N_a, int N_a_pad, int C, __nv_b
 // model.py:117 (norm over C per position), :124 (positive map), :150 (mean_c of the
 // normalised map).  grid (2, N_v): each block owns one half of the positions of one
 // image; 4 channel groups x 128 lanes; every thread streams 16 channels per step.
+// With kWriteBf16 a second sweep emits v_hat = v * rnorm as bf16, transposed to [n][p][c].
 constexpr int kPrepThreads = 512;
 constexpr int kPrepGroups = 4;
 
@@ -87,9 +88,8 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
     __syncthreads();
 
     float ssq = 0.f, dot = 0.f, sum = 0.f;
+    const float* vp = v + (size_t)n * C * P + p;
     if (active) {
-        const float* vp = v + (size_t)n * C * P + p;
-        __nv_bfloat16* op = kWriteBf16 ? vt + ((size_t)n * P + p) * C : nullptr;
         for (int c0 = g * 16; c0 < C; c0 += 16 * kPrepGroups) {
             float x[16];
 #pragma unroll
@@ -100,24 +100,14 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
                 dot = fmaf(x[i], s_a[c0 + i], dot);
                 sum += x[i];
             }
-            if (kWriteBf16) {
-                uint32_t w[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    __nv_bfloat162 h = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
-                    w[i] = *reinterpret_cast<uint32_t*>(&h);
-                }
-                uint4* o = reinterpret_cast<uint4*>(op + c0);
-                o[0] = make_uint4(w[0], w[1], w[2], w[3]);
-                o[1] = make_uint4(w[4], w[5], w[6], w[7]);
-            }
         }
     }
     s_red[(0 * kPrepGroups + g) * 128 + lane] = ssq;
     s_red[(1 * kPrepGroups + g) * 128 + lane] = dot;
     s_red[(2 * kPrepGroups + g) * 128 + lane] = sum;
     __syncthreads();
-    if (g == 0 && active) {
+    float rn = 0.f;
+    if (active) {
         float t0 = 0.f, t1 = 0.f, t2 = 0.f;
 #pragma unroll
         for (int j = 0; j < kPrepGroups; ++j) {
@@ -125,11 +115,32 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
             t1 += s_red[(1 * kPrepGroups + j) * 128 + lane];
             t2 += s_red[(2 * kPrepGroups + j) * 128 + lane];
         }
-        float rn = 1.0f / fmaxf(sqrtf(t0), kNormEps);
-        size_t o = (size_t)n * P + p;
-        rnorm_v[o] = rn;
-        A[o] = t1 * rn;
-        msum[o] = t2 * rn / (float)C;
+        rn = 1.0f / fmaxf(sqrtf(t0), kNormEps);
+        if (g == 0) {
+            size_t o = (size_t)n * P + p;
+            rnorm_v[o] = rn;
+            A[o] = t1 * rn;
+            msum[o] = t2 * rn / (float)C;
+        }
+    }
+    if (kWriteBf16 && active) {
+        // second sweep (L2-resident: this block just streamed these lines): the
+        // normalised map as bf16, K-major [n][p][c] for the tensor-core contraction
+        __nv_bfloat16* op = vt + ((size_t)n * P + p) * C;
+        for (int c0 = g * 16; c0 < C; c0 += 16 * kPrepGroups) {
+            float x[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) x[i] = __ldg(vp + (size_t)(c0 + i) * P) * rn;
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
+                w[i] = *reinterpret_cast<uint32_t*>(&h);
+            }
+            uint4* o = reinterpret_cast<uint4*>(op + c0);
+            o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+            o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+        }
     }
 }
 

@@ -1,0 +1,210 @@
+"""Host side of the similarity + hard-way loss head.
+
+Replaces the body of ``AVENet.forward`` after the backbones (reference ``model.py:114-154``),
+``HardWayAttention.forward`` (``model.py:46-60``) and the ``nn.CrossEntropyLoss`` on the
+logits (``train_hardway_1frame.py:113,130-131``) with calls into libavtubes (sm_100a CUDA).
+The ``N_v x N_a x 14 x 14`` similarity tensor of ``model.py:125`` is never materialised.
+
+Layouts: ``v [N_v, C, P]`` raw visual maps (NCHW with H*W flattened), ``a [N_a, C]`` pooled
+audio embeddings, both fp32 CUDA tensors.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+
+PRECISION = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}
+
+
+@dataclass(frozen=True)
+class HeadConfig:
+    """Scalars of the head.  Reference defaults: ``--epsilon 0.65 --epsilon2 0.4``
+    (``train_hardway_1frame.py:55-56``), ``tau = 0.03`` (``model.py:100``), logit temperature
+    0.07 (``model.py:144``), diagonal mask ``1 - 100*eye`` (``model.py:115``)."""
+    eps: float = 0.65
+    eps2: float = 0.4
+    tau: float = 0.03
+    temp: float = 0.07
+    mask_scale: float = 100.0
+    trimap: bool = True
+    use_neg: bool = True
+    precision: str = "bf16"
+
+
+def audio_normalize(a: torch.Tensor):
+    """``F.normalize(aud, dim=1)`` (``model.py:122``): returns (a_hat, rnorm_a)."""
+    _lib.require_cuda(a)
+    a = a.contiguous().float()
+    n_a, c = a.shape
+    a_hat = torch.empty_like(a)
+    rn = torch.empty(n_a, device=a.device, dtype=torch.float32)
+    lib = _lib.load()
+    _lib.check(lib.avt_audio_normalize(_lib.ptr(a), n_a, c, _lib.ptr(a_hat), _lib.ptr(rn),
+                                       _lib.stream_ptr()), "avt_audio_normalize")
+    return a_hat, rn
+
+
+def audio_normalize_backward(a_hat, rnorm_a, d_ahat):
+    lib = _lib.load()
+    n_a, c = a_hat.shape
+    da = torch.empty_like(a_hat)
+    _lib.check(lib.avt_audio_normalize_backward(_lib.ptr(a_hat), _lib.ptr(rnorm_a),
+                                                _lib.ptr(d_ahat.contiguous()), n_a, c, _lib.ptr(da),
+                                                _lib.stream_ptr()), "avt_audio_normalize_backward")
+    return da
+
+
+def head_forward_raw(v, a_hat, cfg: HeadConfig, pos_idx=None, col_offset=0, want_weighted=False,
+                     for_backward=False):
+    """One ``avt_head_forward`` call.  ``a_hat`` must already be L2-normalised rows.
+    Returns a dict of output tensors (+ the workspace to hand to the backward)."""
+    _lib.require_cuda(v, a_hat)
+    lib = _lib.load()
+    assert v.dtype == torch.float32 and a_hat.dtype == torch.float32
+    assert v.is_contiguous() and a_hat.is_contiguous()
+    n_v, c, p = v.shape
+    n_a = a_hat.shape[0]
+    dev = v.device
+    L = n_a + 1 + (1 if cfg.use_neg else 0)
+    prec = PRECISION[cfg.precision]
+    f32 = dict(device=dev, dtype=torch.float32)
+    out = dict(
+        A=torch.empty(n_v, p, **f32), Pos=torch.empty(n_v, p, **f32), Neg=torch.empty(n_v, p, **f32),
+        logits=torch.empty(n_v, L, **f32), loss_rows=torch.empty(n_v, **f32),
+        loss_sum=torch.empty(1, **f32), rnorm_v=torch.empty(n_v, p, **f32),
+        sim=torch.empty(n_v, n_a, **f32), den=torch.empty(n_v, n_a, **f32),
+        weighted_A=torch.empty(n_v, p, **f32) if want_weighted else None)
+    nbytes = lib.avt_head_workspace_bytes(n_v, n_a, c, p, prec, 1 if for_backward else 0)
+    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    if pos_idx is not None:
+        pos_idx = pos_idx.to(device=dev, dtype=torch.int32).contiguous()
+    with torch.cuda.device(dev):
+        rc = lib.avt_head_forward(
+            _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(pos_idx), int(col_offset),
+            cfg.eps, cfg.eps2, cfg.tau, cfg.temp, cfg.mask_scale, int(cfg.trimap), int(cfg.use_neg),
+            prec, _lib.ptr(out["A"]), _lib.ptr(out["Pos"]), _lib.ptr(out["Neg"]),
+            _lib.ptr(out["logits"]), _lib.ptr(out["loss_rows"]), _lib.ptr(out["loss_sum"]),
+            _lib.ptr(out["weighted_A"]), _lib.ptr(out["rnorm_v"]), _lib.ptr(out["sim"]),
+            _lib.ptr(out["den"]), _lib.ptr(ws), C.c_size_t(nbytes), _lib.stream_ptr())
+    _lib.check(rc, "avt_head_forward")
+    out["workspace"] = ws
+    out["pos_idx"] = pos_idx
+    return out
+
+
+def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits=None, dA=None,
+                      col_offset=0):
+    """One ``avt_head_backward`` call.  Returns (dv [N_v,C,P], d_ahat [N_a,C])."""
+    lib = _lib.load()
+    n_v, c, p = v.shape
+    n_a = a_hat.shape[0]
+    prec = PRECISION[cfg.precision]
+    ws = saved["workspace"]
+    need = lib.avt_head_workspace_bytes(n_v, n_a, c, p, prec, 1)
+    if ws.numel() < need:
+        raise RuntimeError("head_backward_raw: the forward was not run with for_backward=True")
+    dv = torch.empty_like(v)
+    d_ahat = torch.empty_like(a_hat)
+    if dlogits is not None:
+        dlogits = dlogits.contiguous().float()
+    if dA is not None:
+        dA = dA.contiguous().float().view(n_v, p)
+    with torch.cuda.device(v.device):
+        rc = lib.avt_head_backward(
+            _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(saved["pos_idx"]), int(col_offset),
+            cfg.eps, cfg.eps2, cfg.tau, cfg.temp, cfg.mask_scale, int(cfg.trimap), int(cfg.use_neg),
+            prec, _lib.ptr(saved["A"]), _lib.ptr(saved["logits"]), _lib.ptr(saved["loss_rows"]),
+            _lib.ptr(saved["rnorm_v"]), _lib.ptr(saved["sim"]), _lib.ptr(saved["den"]),
+            float(dloss_scale), _lib.ptr(dlogits), _lib.ptr(dA), _lib.ptr(dv), _lib.ptr(d_ahat),
+            _lib.ptr(ws), C.c_size_t(ws.numel()), _lib.stream_ptr())
+    _lib.check(rc, "avt_head_backward")
+    return dv, d_ahat
+
+
+class _HardWayHead(torch.autograd.Function):
+    """autograd wrapper: (v, a) -> (A, logits, Pos, Neg, weighted_A, loss_rows).
+
+    Gradients flow through ``logits``, ``A`` and ``loss_rows`` (the fused
+    CrossEntropyLoss(target 0) per row).  ``Pos`` / ``Neg`` / ``weighted_A`` are returned
+    for inspection exactly like the reference returns them and are non-differentiable here
+    (no reference training script back-propagates through them)."""
+
+    @staticmethod
+    def forward(ctx, v, a, cfg, pos_idx, col_offset, want_weighted):
+        need_grad = v.requires_grad or a.requires_grad
+        v = v.contiguous().float()
+        a_hat, rn_a = audio_normalize(a)
+        out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, want_weighted, for_backward=need_grad)
+        ctx.cfg, ctx.col_offset = cfg, col_offset
+        ctx.saved = out
+        ctx.save_for_backward(v, a_hat, rn_a)
+        w = out["weighted_A"] if want_weighted else out["A"].new_empty(0)
+        ctx.mark_non_differentiable(out["Pos"], out["Neg"], w)
+        return out["A"], out["logits"], out["Pos"], out["Neg"], w, out["loss_rows"]
+
+    @staticmethod
+    def backward(ctx, gA, glogits, gPos, gNeg, gW, gloss_rows):
+        v, a_hat, rn_a = ctx.saved_tensors
+        dlogits = glogits
+        # d loss_rows[n] / d logits[n, :] = softmax - onehot(0); fold a row-wise upstream
+        # gradient into dlogits unless it is one uniform scalar (the mean / sum case)
+        scale = 0.0
+        if gloss_rows is not None:
+            g = gloss_rows.contiguous().float()
+            lg = ctx.saved["logits"]
+            sm = torch.softmax(lg, dim=1)
+            sm[:, 0] -= 1.0
+            extra = sm * g[:, None]
+            dlogits = extra if dlogits is None else dlogits + extra
+        dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, scale, dlogits, gA,
+                                       ctx.col_offset)
+        da = audio_normalize_backward(a_hat, rn_a, d_ahat)
+        return dv, da, None, None, None, None
+
+
+class _HardWayLoss(torch.autograd.Function):
+    """(v, a) -> mean_n CrossEntropy(logits[n], 0), fully fused: the only upstream gradient
+    is one scalar, so the backward needs no dlogits tensor at all."""
+
+    @staticmethod
+    def forward(ctx, v, a, cfg, pos_idx, col_offset, divisor):
+        need_grad = v.requires_grad or a.requires_grad
+        v = v.contiguous().float()
+        a_hat, rn_a = audio_normalize(a)
+        out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=need_grad)
+        ctx.cfg, ctx.col_offset, ctx.divisor = cfg, col_offset, divisor
+        ctx.saved = out
+        ctx.save_for_backward(v, a_hat, rn_a)
+        return out["loss_sum"][0] / divisor
+
+    @staticmethod
+    def backward(ctx, gloss):
+        v, a_hat, rn_a = ctx.saved_tensors
+        # one host read of the scalar upstream gradient (1.0 for loss.backward())
+        scale = float(gloss) / ctx.divisor
+        dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, scale, None, None, ctx.col_offset)
+        da = audio_normalize_backward(a_hat, rn_a, d_ahat)
+        return dv, da, None, None, None, None
+
+
+def hardway_head(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0,
+                 return_weighted=False):
+    """v [N_v,C,P] (or [N_v,C,H,W]), a [N_a,C] -> (A [N_v,P], logits [N_v,N_a+1(+1)], Pos, Neg,
+    weighted_A or None, loss_rows [N_v])."""
+    if v.dim() == 4:
+        v = v.flatten(2)
+    A, logits, Pos, Neg, w, loss_rows = _HardWayHead.apply(v, a, cfg, pos_idx, col_offset,
+                                                           return_weighted)
+    return A, logits, Pos, Neg, (w if return_weighted else None), loss_rows
+
+
+def hardway_loss(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0, divisor=None):
+    """Fused ``CrossEntropyLoss()(logits, zeros)`` of the head (``train_hardway_1frame.py:130-131``):
+    mean over the N_v rows (or sum / divisor for row-sharded ranks)."""
+    if v.dim() == 4:
+        v = v.flatten(2)
+    return _HardWayLoss.apply(v, a, cfg, pos_idx, col_offset, float(divisor or v.shape[0]))

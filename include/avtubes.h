@@ -125,6 +125,12 @@ int avt_eval_maps(const float* maps14, int N,
                   float* up224, uint8_t* mask,
                   int32_t* inter_w, int32_t* union_w, double* ciou, void* stream);
 
+/* Evaluator.cal_CIOU(infer, gtmap, thres) (utils.py:209-214) on N ready-made 224x224 fp32
+ * maps: infer_map = (infer >= thres); gt = gt_w / gt_den with gt_w uint8 weights.
+ * inter_w / union_w / ciou as in avt_eval_maps. */
+int avt_ciou_counts(const float* infer, float thres, const uint8_t* gt_w, int gt_den, int N,
+                    int32_t* inter_w, int32_t* union_w, double* ciou, void* stream);
+
 /* utils.py:241-274 / 276-309: boxes -> dense weight map [N,224,224] uint8 */
 int avt_rasterise_gt(const int16_t* boxes, const uint8_t* box_count, int N, int max_boxes,
                      int gt_mode, uint8_t* gt_dense, void* stream);

@@ -1,0 +1,159 @@
+"""GPU parity of the evaluation kernels: bit-exact masks / counts / cIoU against the CPU
+oracle on identical maps; within 1e-3 of the reference's cv2-based golden numbers."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import eval_oracle as eo
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+EVAL = np.load(os.path.join(GOLD, "eval_golden.npz"))
+
+
+def _eval_inputs():
+    n, seed = EVAL["eval/meta"]
+    maps = eo.synthetic_maps(int(n), int(seed))
+    maps[5] = 0.25; maps[6] = -0.25; maps[7] = np.round(maps[7], 1)
+    boxes = json.loads(str(EVAL["eval/boxes_json"]))
+    names = [str(x) for x in EVAL["eval/names"]]
+    return maps, [boxes[k] for k in names]
+
+
+def _check_against_oracle(maps, gts_w, gt_den, res, idx=None):
+    idx = range(len(maps)) if idx is None else idx
+    up = res["up224"].cpu().numpy(); mk = res["mask"].cpu().numpy()
+    iw = res["inter_w"].cpu().numpy(); uw = res["union_w"].cpu().numpy(); ci = res["ciou"].cpu().numpy()
+    for i in idx:
+        o = eo.evaluate_map(maps[i], gts_w[i], gt_den)
+        assert np.array_equal(up[i], o["up224"]), f"map {i}: upsample differs"
+        assert np.array_equal(mk[i], o["mask"]), f"map {i}: mask differs in {(mk[i] != o['mask']).sum()} px"
+        assert iw[i] == o["inter_w"] and uw[i] == o["union_w"]
+        assert (np.isnan(ci[i]) and np.isnan(o["ciou"])) or ci[i] == o["ciou"]
+
+
+def test_golden_case_bit_exact_vs_oracle_and_close_to_reference():
+    from audio_visual_tubes_b200 import evaluate_maps
+    maps, boxes = _eval_inputs()
+    n = len(boxes)
+    r = evaluate_maps(maps, boxes=boxes, gt_mode="vggss", want_up224=True, want_mask=True)
+    gts = [eo.rasterise_gt(b, "vggss")[0] for b in boxes]
+    _check_against_oracle(maps, gts, 1, r)
+    o = eo.evaluate_maps(maps, gts, 1)
+    assert np.array_equal(r["counts"].cpu().numpy(), o["counts"])
+    assert r["ciou_at_half"] == o["ciou_at_half"]
+    assert abs(r["auc"] - o["auc"]) < 1e-12
+    # against the reference itself (cv2 resize differs by <= 1 ulp -> <= a few pixels)
+    g = EVAL["eval/ciou"]
+    c = r["ciou"].cpu().numpy()
+    assert np.all((np.isnan(c) & np.isnan(g)) | (np.abs(c - g) <= 1e-3))
+    assert abs(r["ciou_at_half"] - float(EVAL["eval/ciou_at_half"])) <= 1e-3 + 1.0 / n
+    assert abs(r["auc"] - float(EVAL["eval/auc"])) <= 1e-3 + 1.0 / n
+    assert np.abs(r["up224"][:4].cpu().numpy() - EVAL["eval/up224_cv2_first4"]).max() <= 1.2e-7
+    gmask = np.unpackbits(EVAL["eval/mask_packed"])[: n * 224 * 224].reshape(n, 224, 224)
+    assert ((r["mask"].cpu().numpy() != gmask).reshape(n, -1).sum(1) <= 4).all()
+    # dense-GT mode is the same computation
+    gd = np.stack(gts)
+    r2 = evaluate_maps(maps, gt_dense=gd, want_up224=True, want_mask=True)
+    for k in ("ciou", "inter_w", "union_w", "mask", "up224"):
+        assert torch.equal(r[k].nan_to_num(-1), r2[k].nan_to_num(-1)) if k == "ciou" else torch.equal(r[k], r2[k])
+
+
+def test_adversarial_maps_bit_exact():
+    """Ties, huge / tiny scales, negatives, steps, outliers: the order statistic, the
+    normalisation and the strict '>' must agree with numpy bit for bit."""
+    from audio_visual_tubes_b200 import evaluate_maps
+    rng = np.random.default_rng(7)
+    base = eo.synthetic_maps(40, 3)
+    maps = [base[0], np.round(base[1], 1), np.round(base[2], 2), base[3] * 1e30, base[4] * 1e-30,
+            -base[5], base[6] - 0.5, base[7] * 1000 - 300, np.zeros((14, 14), np.float32),
+            np.full((14, 14), -1.5, np.float32), np.full((14, 14), 2.0, np.float32),
+            (rng.uniform(size=(14, 14)) > 0.5).astype(np.float32),
+            (rng.uniform(size=(14, 14)) > 0.9).astype(np.float32) * 5,
+            np.tile(np.arange(14, dtype=np.float32), (14, 1)),
+            np.tile(np.arange(14, dtype=np.float32), (14, 1)).T * -3,
+            rng.standard_normal((14, 14)).astype(np.float32),
+            rng.standard_normal((14, 14)).astype(np.float32) * 1e-3 + 1000.0,
+            np.where(rng.uniform(size=(14, 14)) > 0.97, 1e6, 0.5).astype(np.float32),
+            base[8] * 0 + np.float32(0.1) + (rng.uniform(size=(14, 14)) > 0.5) * np.float32(1e-7)]
+    maps += [base[i] for i in range(9, 40)]
+    maps = np.stack([m.astype(np.float32) for m in maps])
+    boxes = [[[0.1 + 0.01 * (i % 7), 0.2, 0.6, 0.9]] for i in range(len(maps))]
+    gts = [eo.rasterise_gt(b, "vggss")[0] for b in boxes]
+    r = evaluate_maps(maps, boxes=boxes, want_up224=True, want_mask=True)
+    _check_against_oracle(maps, gts, 1, r)
+
+
+def test_gt_modes_and_rasterise():
+    from audio_visual_tubes_b200 import rasterise_gt, evaluate_maps
+    maps, boxes = _eval_inputs()
+    n = len(boxes)
+    g = rasterise_gt(boxes, "vggss").cpu().numpy()
+    gold = np.unpackbits(EVAL["eval/gt_packed"])[: n * 224 * 224].reshape(n, 224, 224)
+    assert np.array_equal(g, gold)
+    fb = [EVAL["gt/flickr_boxes"].tolist()]
+    w = rasterise_gt(fb, "flickr").cpu().numpy()[0]
+    assert np.array_equal(w / 2.0, EVAL["gt/flickr"])
+    w = rasterise_gt(fb, "flickr_frame").cpu().numpy()[0]
+    assert np.array_equal(w.astype(np.float64), EVAL["gt/flickr_frame"])
+    # half-integer weights (Flickr): counts stay exact
+    m = maps[:3]
+    for mode in ("flickr", "flickr_frame"):
+        gw, den = eo.rasterise_gt(fb[0], mode)
+        r = evaluate_maps(m, boxes=fb * 3, gt_mode=mode, want_up224=True, want_mask=True)
+        _check_against_oracle(m, [gw] * 3, den, r)
+
+
+def test_evaluator_api_and_mtc():
+    from audio_visual_tubes_b200 import Evaluator, mTC
+    n = int(EVAL["eval/meta"][0])
+    gmask = np.unpackbits(EVAL["eval/mask_packed"])[: n * 224 * 224].reshape(n, 224, 224)
+    ggt = np.unpackbits(EVAL["eval/gt_packed"])[: n * 224 * 224].reshape(n, 224, 224)
+    ev = Evaluator()
+    for i in (0, 1, 2, 3):
+        c, inter, union = ev.cal_CIOU(gmask[i].astype(np.float32), ggt[i].astype(np.float64), 0.5)
+        assert inter == EVAL["eval/inter"][i] and union == EVAL["eval/union"][i]
+        assert c == EVAL["eval/ciou"][i]
+    assert len(ev.ciou) == 4
+    o_counts, o_res = eo.success_curve(ev.ciou)
+    assert abs(ev.cal_AUC() - eo.auc_trapezoid(o_res)) < 1e-12
+    assert ev.final() == eo.ciou_at_half(ev.ciou)
+    ev.clear(); assert ev.ciou == []
+    # Flickr half weights through the reference API
+    c, inter, union = Evaluator().cal_CIOU(gmask[0].astype(np.float32), EVAL["gt/flickr"], 0.5)
+    cf, interf, unionf = eo.cal_ciou_float(gmask[0].astype(np.float32), EVAL["gt/flickr"], 0.5)
+    assert (c, inter, union) == (cf, interf, unionf)
+    got = float(mTC(list(gmask[16:24].astype(np.float64)), [None] * 8))
+    assert abs(got - float(EVAL["eval/mtc_16_24"])) < 1e-6
+
+
+def test_config3_full_size_properties_and_sampled_parity():
+    """BASELINE config 3: 5158 synthetic maps.  Oracle parity on a sample; size-independent
+    properties on all: mask popcount is at most 25087 unless degenerate, cIoU in [0,1] or NaN,
+    counts of the success curve are non-increasing, permutation invariance."""
+    from audio_visual_tubes_b200 import evaluate_maps
+    n = 5158
+    maps = eo.synthetic_maps(n, 0)
+    rng = np.random.default_rng(1)
+    boxes = []
+    for i in range(n):
+        x0, y0 = rng.uniform(0, 0.7, 2); w, h = rng.uniform(0.1, 0.3, 2)
+        boxes.append([[x0, y0, x0 + w, y0 + h]])
+    r = evaluate_maps(maps, boxes=boxes, want_up224=True, want_mask=True)
+    pop = r["mask"].view(n, -1).sum(1, dtype=torch.int32).cpu().numpy()
+    assert pop.max() <= 25087 and pop.min() >= 25000
+    c = r["ciou"].cpu().numpy()
+    assert np.all((c >= 0) & (c <= 1))
+    cnt = r["counts"].cpu().numpy()
+    assert cnt[0] == n and np.all(np.diff(cnt) <= 0)
+    idx = list(range(0, n, 97))
+    gts = {i: eo.rasterise_gt(boxes[i], "vggss")[0] for i in idx}
+    _check_against_oracle(maps, gts, 1, r, idx)
+    perm = rng.permutation(n)
+    r2 = evaluate_maps(maps[perm], boxes=[boxes[i] for i in perm])
+    assert np.array_equal(r2["ciou"].cpu().numpy(), c[perm])
+    assert r2["auc"] == r["auc"] and r2["ciou_at_half"] == r["ciou_at_half"]

@@ -1,0 +1,213 @@
+"""GPU parity of the similarity + hard-way loss head: libavtubes (through the C ABI) against
+the golden vectors of the unmodified reference and against the CPU oracle.
+
+Tolerances (BASELINE.json north_star): logits / loss / maps within 2e-3 relative for the
+bf16 tensor-core path; the fp32 path is held to fp32 round-off."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from inputs import head_features
+from oracle import head_oracle as ho
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+HEAD = np.load(os.path.join(GOLD, "head_golden.npz"))
+HEAD_CASES = [("cfg1_relu", "relu"), ("cfg1_mix", "mix"), ("b32_mix", "mix"),
+              ("b16_notrimap", "mix"), ("b16_noneg", "mix"), ("b8_signed", "signed")]
+# (max-norm relative tolerance of logits / maps, gradient tolerance)
+TOL = {"fp32": (2e-5, 2e-4), "bf16": (2e-3, 2e-3)}
+PRECISIONS = ["fp32", "bf16"]
+
+
+def rel(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+
+
+def relnorm(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-30)
+
+
+def run_head(v, a, precision, trimap=True, use_neg=True, pos=None, col_offset=0, grad=False,
+             dlogits=None, dA=None, loss_scale=1.0, weighted=True):
+    from audio_visual_tubes_b200 import HeadConfig, hardway_head
+    cfg = HeadConfig(trimap=trimap, use_neg=use_neg, precision=precision)
+    vt = torch.tensor(v, device="cuda", requires_grad=grad)
+    at = torch.tensor(a, device="cuda", requires_grad=grad)
+    pt = None if pos is None else torch.tensor(pos, device="cuda", dtype=torch.int32)
+    A, logits, Pos, Neg, wA, loss_rows = hardway_head(vt, at, cfg, pt, col_offset, return_weighted=weighted)
+    out = dict(A=A, logits=logits, Pos=Pos, Neg=Neg, weighted_A=wA, loss_rows=loss_rows)
+    res = {k: (None if t is None else t.detach().cpu().numpy()) for k, t in out.items()}
+    if grad:
+        total = loss_scale * loss_rows.mean()
+        if dlogits is not None:
+            total = total + (torch.tensor(dlogits, device="cuda") * logits).sum()
+        if dA is not None:
+            total = total + (torch.tensor(dA, device="cuda") * A).sum()
+        total.backward()
+        res["dv"] = vt.grad.cpu().numpy()
+        res["da"] = at.grad.cpu().numpy()
+    torch.cuda.synchronize()
+    return res
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("name,mode", HEAD_CASES)
+def test_forward_matches_reference_golden(name, mode, precision):
+    n, seed, trimap, neg = HEAD[f"{name}/meta"]
+    v, a = head_features(n, n, seed, mode)
+    r = run_head(v, a, precision, bool(trimap), bool(neg))
+    tol = TOL[precision][0]
+    assert r["logits"].shape == (n, n + 1 + int(neg))
+    assert rel(r["A"], HEAD[f"{name}/A"].reshape(n, -1)) < tol
+    assert rel(r["logits"], HEAD[f"{name}/logits"]) < tol
+    assert rel(r["weighted_A"], HEAD[f"{name}/weighted_A"].reshape(n, -1)) < max(tol, 5e-5)
+    # Pos / Neg are sigmoids of (A - eps)/tau: an error dA becomes dA/tau/4 absolute
+    ptol = 2e-5 if precision == "fp32" else 2e-3
+    assert np.abs(r["Pos"] - HEAD[f"{name}/Pos"].reshape(n, -1)).max() < ptol
+    assert np.abs(r["Neg"] - HEAD[f"{name}/Neg"].reshape(n, -1)).max() < ptol
+    loss = float(r["loss_rows"].mean())
+    assert abs(loss - float(HEAD[f"{name}/loss"])) < tol * max(1.0, abs(loss))
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("name,mode", HEAD_CASES)
+def test_backward_matches_reference_autograd(name, mode, precision):
+    n, seed, trimap, neg = HEAD[f"{name}/meta"]
+    v, a = head_features(n, n, seed, mode)
+    r = run_head(v, a, precision, bool(trimap), bool(neg), grad=True)
+    tol = TOL[precision][1]
+    assert relnorm(r["dv"][:, ::16, ::7], HEAD[f"{name}/dv_sub"]) < tol
+    assert rel(np.sqrt((r["dv"].astype(np.float64) ** 2).sum((1, 2))), HEAD[f"{name}/dv_norm"]) < tol
+    assert relnorm(r["da"], HEAD[f"{name}/da"]) < tol
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_backward_with_external_grads_vs_oracle(precision):
+    """dlogits and dA upstream gradients (not only the fused CE) against fp64 autograd."""
+    n = 24
+    v, a = head_features(n, n, 21, "mix")
+    rng = np.random.default_rng(5)
+    dlog = (rng.standard_normal((n, n + 2)) * 0.05).astype(np.float32)
+    dA = (rng.standard_normal((n, 196)) * 0.01).astype(np.float32)
+    r = run_head(v, a, precision, grad=True, dlogits=dlog, dA=dA, loss_scale=0.5)
+    _, dv, da = ho.head_forward_backward_torch(v, a, dlogits=dlog, dA=dA, loss_scale=0.5)
+    tol = TOL[precision][1]
+    assert relnorm(r["dv"], dv) < tol
+    assert relnorm(r["da"], da) < tol
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("mode", ["relu", "mix"])
+def test_config2_b128_vs_oracle(mode, precision):
+    """BASELINE config 2 shape (B=128): forward + backward against the oracle."""
+    n = 128
+    v, a = head_features(n, n, 31, mode)
+    r = run_head(v, a, precision, grad=True)
+    o, dv, da = ho.head_forward_backward_torch(v, a, dtype="float64", threads=8)
+    tol, gtol = TOL[precision]
+    assert rel(r["logits"], o["logits"]) < tol
+    assert rel(r["A"], o["A"]) < tol
+    assert abs(r["loss_rows"].mean() - o["loss"]) < tol * max(1.0, abs(o["loss"]))
+    assert relnorm(r["dv"], dv) < gtol
+    assert relnorm(r["da"], da) < gtol
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_row_shard_of_b1024(precision):
+    """Config 5 as one rank sees it: 64 visual rows against all 1024 audio columns, the
+    positives starting at column 320 (col_offset).  Must equal rows 320..383 of the full
+    problem, which the oracle evaluates with pos = 320 + arange."""
+    n_a, n_v, off = 1024, 64, 320
+    v_all, a = head_features(n_v, n_a, 41, "mix")
+    pos = off + np.arange(n_v)
+    # make v's own positives the shifted columns (head_features built them for pos = arange)
+    o = ho.head_forward(v_all, a, pos=pos, dtype=np.float64)
+    r = run_head(v_all, a, precision, col_offset=off)
+    tol = TOL[precision][0]
+    assert rel(r["logits"], o["logits"]) < tol
+    assert rel(r["A"], o["A"]) < tol
+    r2 = run_head(v_all, a, precision, pos=pos)              # explicit pos_idx, same thing
+    assert np.array_equal(r["logits"], r2["logits"])
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_tube_mode_and_broadcast(precision):
+    from audio_visual_tubes_b200 import HardWayAttention
+    b, t, seed = HEAD["tube_b2t4/meta"]
+    n = b * t
+    v, a = head_features(n, b, seed, "mix")
+    vid = torch.tensor(v.reshape(b, t, 512, 14, 14).transpose(0, 2, 1, 3, 4).copy(), device="cuda")
+    aud = torch.tensor(np.repeat(a, t, axis=0), device="cuda")           # train_3D.py:129-130
+    att = HardWayAttention(precision)
+    A, logits = att(aud, vid)
+    tol = TOL[precision][0]
+    assert A.shape == (n, 1, 14, 14) and logits.shape == (n, n + 2)
+    assert rel(A.cpu().numpy().reshape(n, -1), HEAD["tube_b2t4/A"].reshape(n, -1)) < tol
+    assert rel(logits.cpu().numpy(), HEAD["tube_b2t4/logits"]) < tol
+    # test time: one audio row against T frames (train_3D.py:153-154)
+    A1, l1 = att(torch.tensor(a[:1], device="cuda"), vid[:1])
+    assert rel(l1.cpu().numpy(), HEAD["tube_b2t4/logits_bcast"]) < tol
+    assert rel(A1.cpu().numpy().reshape(t, -1), HEAD["tube_b2t4/A_bcast"].reshape(t, -1)) < tol
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("n_v,n_a", [(1, 1), (3, 5), (7, 130), (33, 17), (2, 257)])
+def test_ragged_shapes(n_v, n_a, precision):
+    v, a = head_features(n_v, n_a, 51, "mix")
+    pos = np.arange(n_v) % n_a
+    o = ho.head_forward(v, a, pos=pos, dtype=np.float64)
+    r = run_head(v, a, precision, pos=pos)
+    assert rel(r["logits"], o["logits"]) < TOL[precision][0]
+
+
+def test_fused_loss_matches_head_and_is_linear_in_scale():
+    from audio_visual_tubes_b200 import HeadConfig, hardway_loss
+    v, a = head_features(16, 16, 61, "mix")
+    cfg = HeadConfig(precision="fp32")
+    vt = torch.tensor(v, device="cuda", requires_grad=True)
+    at = torch.tensor(a, device="cuda", requires_grad=True)
+    loss = hardway_loss(vt, at, cfg)
+    (3.0 * loss).backward()
+    o, dv, da = ho.head_forward_backward_torch(v, a, loss_scale=3.0)
+    assert abs(float(loss) - o["loss"]) < 1e-5 * max(1, abs(o["loss"]))
+    assert relnorm(vt.grad.cpu().numpy(), dv) < 2e-4
+    assert relnorm(at.grad.cpu().numpy(), da) < 2e-4
+
+
+def test_errors_are_loud():
+    from audio_visual_tubes_b200 import HeadConfig, hardway_head
+    v, a = head_features(2, 2, 1, "relu")
+    with pytest.raises(RuntimeError):                       # CPU tensors: no fallback
+        hardway_head(torch.tensor(v), torch.tensor(a), HeadConfig())
+    with pytest.raises(RuntimeError):                       # C not a multiple of 64
+        hardway_head(torch.zeros(2, 100, 196, device="cuda"), torch.zeros(2, 100, device="cuda"),
+                     HeadConfig(precision="fp32"))
+
+
+def test_avenet_contract():
+    """AVENet(args, pretrained).forward(image, audio) -> (A, logits, Pos, Neg), model.py:112-154."""
+    import types
+    from audio_visual_tubes_b200 import AVENet
+    args = types.SimpleNamespace(epsilon=0.65, epsilon2=0.4, tri_map=True, Neg=True)
+    torch.manual_seed(0)
+    net = AVENet(args, False).cuda().eval()
+    img = torch.randn(4, 3, 224, 224, device="cuda")
+    aud = torch.randn(4, 1, 257, 300, device="cuda")
+    with torch.no_grad():
+        A, logits, Pos, Neg = net(img, aud)
+        fi, fa = net.features(img, aud)
+    assert A.shape == (4, 1, 14, 14) and logits.shape == (4, 6)
+    assert Pos.shape == (4, 1, 14, 14) and Neg.shape == (4, 1, 14, 14)
+    o = ho.head_forward(fi.flatten(2).cpu().numpy(), fa.cpu().numpy(), dtype=np.float64)
+    assert rel(logits.cpu().numpy(), o["logits"]) < 2e-3
+    assert rel(A.cpu().numpy().reshape(4, -1), o["A"]) < 2e-3
+    net.train()
+    loss = net.loss(img, aud)
+    loss.backward()
+    assert torch.isfinite(loss) and net.imgnet.conv1.weight.grad is not None
