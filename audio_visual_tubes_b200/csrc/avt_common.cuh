@@ -106,7 +106,7 @@ int launch_row_grad(const float* A, const float* logits, const float* loss_rows,
                     cudaStream_t st);
 int launch_bwd_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
-                    HeadParams hp, const float* sim, const float* den, const float* gsim,
+                    HeadParams hp, const float* gsim,
                     const float* GA, float* dvh, float* dah, cudaStream_t st);
 int launch_dv_finish(const float* v, const float* rnorm_v, int N_v, int C, int P, float* dv,
                      cudaStream_t st);
@@ -115,7 +115,7 @@ int launch_dv_finish(const float* v, const float* rnorm_v, int N_v, int C, int P
 int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
-int launch_bwd_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, __nv_bfloat16* at_bf,
+int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, __nv_bfloat16* at_bf,
                     __nv_bfloat16* g_bf, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C,
                     int P, HeadParams hp, const float* sim, const float* den, const float* gsim,

@@ -305,7 +305,7 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
                     on = (pr > thr) || (pr >= 1.0f);
                 }
                 const uint32_t ball = __ballot_sync(0xffffffffu, on);
-                const int j = __ffs(ball) - 1;                   // lane 31 is 'on' at the latest
+                const int j = ball ? __ffs(ball) - 1 : 32;       // 32: every probe was valid and off
                 if (j == 0) { hi = lo; }
                 else {
                     const uint64_t nh = (uint64_t)lo + (uint64_t)j * step;

@@ -142,8 +142,8 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
     AVT_CHECK_CUDA(cudaMemsetAsync(d_ahat, 0, (size_t)N_a * C * sizeof(float), st));
     if (precision == AVT_PRECISION_FP32) {
         AVT_CHECK_CUDA(cudaMemsetAsync(dv, 0, (size_t)N_v * C * P * sizeof(float), st));
-        rc = launch_bwd_fp32(v, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a, C, P, hp, sim, den,
-                             gsim, GA, dv, d_ahat, st);
+        rc = launch_bwd_fp32(v, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a, C, P, hp, gsim, GA, dv,
+                             d_ahat, st);
         if (rc != AVT_OK) return rc;
         return launch_dv_finish(v, rnorm_v, N_v, C, P, dv, st);
     }
@@ -156,6 +156,6 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
     __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
     __nv_bfloat16* at_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.at_bf);
     __nv_bfloat16* g_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.g_bf);
-    return launch_bwd_bf16(vt, a_bf, at_bf, g_bf, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
+    return launch_bwd_bf16(v, vt, a_bf, at_bf, g_bf, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
                            n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, st);
 }

@@ -212,7 +212,6 @@ __global__ void __launch_bounds__(kSimThreads)
 bwd_fp32_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
                 const float* __restrict__ rnorm_v, const int32_t* __restrict__ pos_idx,
                 int col_offset, int N_a, int C, int P, HeadParams hp,
-                const float* __restrict__ sim, const float* __restrict__ den,
                 const float* __restrict__ gsim, const float* __restrict__ GA,
                 float* __restrict__ dvh, float* __restrict__ dah) {
     extern __shared__ float smem[];
@@ -221,6 +220,8 @@ bwd_fp32_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
     float* G_s = a_s + (size_t)C * kKT;                  // [kKT][PS]
     float* v_s = G_s + (size_t)kKT * PS;                 // [kBwdChunk][PS]
     float* rn_s = v_s + (size_t)kBwdChunk * PS;          // [P]
+    float* red_s = rn_s + P;                             // [2][warps][kKT]
+    float* sd_s = red_s + 2 * (kSimThreads / 32) * kKT;   // [2][kKT] pooled sim, den
     const int n = blockIdx.y, k0 = blockIdx.x * kKT;
     const int p = threadIdx.x;
     const int pos = pos_idx ? pos_idx[n] : col_offset + n;
@@ -228,18 +229,46 @@ bwd_fp32_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
     for (int i = threadIdx.x; i < P; i += blockDim.x) rn_s[i] = rnorm_v[(size_t)n * P + i];
     __syncthreads();
 
+    // S for this block's 16 audio rows, then the pooled sim / den recomputed in fp32 here
+    // (self-consistent gradient; the saved forward values may come from the bf16 path)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float itau = 1.0f / hp.tau;
+    float S[kKT], W[kKT];
+    if (p < P) {
+        dot_rows(v + (size_t)n * C * P + p, C, P, a_s, rn_s[p], S);
+#pragma unroll
+        for (int k = 0; k < kKT; ++k) W[k] = sigmoid_acc((S[k] - hp.eps) * itau);
+    } else {
+#pragma unroll
+        for (int k = 0; k < kKT; ++k) { S[k] = 0.f; W[k] = 0.f; }
+    }
+#pragma unroll
+    for (int k = 0; k < kKT; ++k) {
+        float a = warp_sum(W[k] * S[k]), b = warp_sum(W[k]);
+        if (lane == 0) {
+            red_s[(0 * (kSimThreads / 32) + warp) * kKT + k] = a;
+            red_s[(1 * (kSimThreads / 32) + warp) * kKT + k] = b;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < kKT) {
+        float a = 0.f, b = 0.f;
+#pragma unroll
+        for (int w = 0; w < kSimThreads / 32; ++w) {
+            a += red_s[(0 * (kSimThreads / 32) + w) * kKT + threadIdx.x];
+            b += red_s[(1 * (kSimThreads / 32) + w) * kKT + threadIdx.x];
+        }
+        sd_s[threadIdx.x] = a / b;
+        sd_s[kKT + threadIdx.x] = b;
+    }
+    __syncthreads();
     float G[kKT];
     if (p < P) {
-        float S[kKT];
-        dot_rows(v + (size_t)n * C * P + p, C, P, a_s, rn_s[p], S);
-        const float itau = 1.0f / hp.tau;
 #pragma unroll
         for (int k = 0; k < kKT; ++k) {
             float g = 0.f;
             if (k0 + k < N_a) {
-                float w = sigmoid_acc((S[k] - hp.eps) * itau);
-                float sm = sim[(size_t)n * N_a + k0 + k];
-                float dn = den[(size_t)n * N_a + k0 + k];
+                const float w = W[k], sm = sd_s[k], dn = sd_s[kKT + k];
                 g = gsim[(size_t)n * N_a + k0 + k] * (w + (S[k] - sm) * w * (1.0f - w) * itau) / dn;
                 if (k0 + k == pos) g += GA[(size_t)n * P + p];
             }
@@ -250,7 +279,6 @@ bwd_fp32_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
 #pragma unroll
         for (int k = 0; k < kKT; ++k) G[k] = 0.f;
     }
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int c0 = 0; c0 < C; c0 += kBwdChunk) {
         __syncthreads();
         for (int i = threadIdx.x; i < kBwdChunk * P; i += blockDim.x) {
@@ -293,15 +321,16 @@ bwd_fp32_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
 
 int launch_bwd_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
-                    HeadParams hp, const float* sim, const float* den, const float* gsim,
+                    HeadParams hp, const float* gsim,
                     const float* GA, float* dvh, float* dah, cudaStream_t st) {
     const int PS = P + 1;
-    size_t smem = ((size_t)C * kKT + (size_t)kKT * PS + (size_t)kBwdChunk * PS + P) * sizeof(float);
+    size_t smem = ((size_t)C * kKT + (size_t)kKT * PS + (size_t)kBwdChunk * PS + P +
+                   2 * (kSimThreads / 32) * kKT + 2 * kKT) * sizeof(float);
     AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)smem));
     dim3 grid((N_a + kKT - 1) / kKT, N_v);
     bwd_fp32_kernel<<<grid, kSimThreads, smem, st>>>(v, a_hat, rnorm_v, pos_idx, col_offset, N_a, C, P,
-                                                    hp, sim, den, gsim, GA, dvh, dah);
+                                                    hp, gsim, GA, dvh, dah);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
