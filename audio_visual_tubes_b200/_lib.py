@@ -25,6 +25,9 @@ SIGNATURES = {
     "avt_version": (_i, []),
     "avt_last_error": (C.c_char_p, []),
     "avt_device_ok": (_i, []),
+    "avt_launch_count": (C.c_longlong, []),
+    "avt_profile_enable": (_i, [_i]),
+    "avt_profile_read": (_i, [_i, _p, _p]),
     "avt_audio_normalize": (_i, [_p, _i, _i, _p, _p, _p]),
     "avt_audio_normalize_backward": (_i, [_p, _p, _p, _i, _i, _p, _p]),
     "avt_head_workspace_bytes": (_z, [_i, _i, _i, _i, _i, _i]),
@@ -84,3 +87,26 @@ def require_cuda(*tensors):
         if t is not None and not t.is_cuda:
             raise RuntimeError("libavtubes runs on the GPU only: got a CPU tensor "
                                "(there is no CPU fallback; move inputs to cuda)")
+
+
+PROF_SLOTS = {"prep": 0, "sim": 1, "finish": 2, "row_grad": 3, "bwd_g": 4, "bwd_dv": 5,
+              "bwd_da": 6, "dv_finish": 7, "eval": 8}
+
+
+def profile_enable(on: bool = True):
+    check(load().avt_profile_enable(int(on)), "avt_profile_enable")
+
+
+def profile_read():
+    """{stage: (total_ms, intervals)} since the last profile_enable()."""
+    lib = load()
+    out = {}
+    for name, slot in PROF_SLOTS.items():
+        ms, n = C.c_double(0.0), C.c_int(0)
+        check(lib.avt_profile_read(slot, C.byref(ms), C.byref(n)), "avt_profile_read")
+        out[name] = (ms.value, n.value)
+    return out
+
+
+def launch_count() -> int:
+    return int(load().avt_launch_count())

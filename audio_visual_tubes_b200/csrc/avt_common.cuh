@@ -14,6 +14,21 @@ namespace avt {
 
 void set_error(const char* fmt, ...);
 
+// Launch counter and optional per-stage device timing (avt_profile_* in avtubes.h).
+// Stage slots; the events are recorded on the stream the stage is launched on.
+enum ProfSlot {
+    kProfPrep = 0, kProfSim = 1, kProfFinish = 2, kProfRowGrad = 3, kProfBwdG = 4,
+    kProfBwdDv = 5, kProfBwdDa = 6, kProfDvFinish = 7, kProfEval = 8, kProfSlots = 9
+};
+void count_launch();
+void prof_begin(int slot, cudaStream_t st);
+void prof_end(int slot, cudaStream_t st);
+struct ProfScope {
+    int slot; cudaStream_t st;
+    ProfScope(int s, cudaStream_t t) : slot(s), st(t) { prof_begin(slot, st); }
+    ~ProfScope() { prof_end(slot, st); }
+};
+
 #define AVT_CHECK_CUDA(expr)                                                        \
     do {                                                                            \
         cudaError_t _e = (expr);                                                    \
@@ -34,6 +49,7 @@ void set_error(const char* fmt, ...);
 
 #define AVT_LAUNCH_CHECK()                                                          \
     do {                                                                            \
+        avt::count_launch();                                                        \
         cudaError_t _e = cudaGetLastError();                                        \
         if (_e != cudaSuccess) {                                                    \
             avt::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), \

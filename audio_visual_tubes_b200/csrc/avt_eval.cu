@@ -525,6 +525,7 @@ extern "C" int avt_eval_maps(const float* maps14, int N, const uint8_t* gt_dense
     AVT_CHECK_CUDA(cudaGetDevice(&dev));
     AVT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int grid = N < sms * 6 ? N : sms * 6;           // 6 resident blocks per SM
+    ProfScope _ps(kProfEval, st);
     if (gt_dense) {
         AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<true>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -101,6 +101,7 @@ sim_fp32_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
 int launch_sim_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st) {
+    ProfScope _ps(kProfSim, st);
     const int L = N_a + 1 + (hp.use_neg ? 1 : 0);
     size_t smem = ((size_t)C * kKT + 2 * (kSimThreads / 32) * kKT) * sizeof(float);
     AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -194,6 +195,7 @@ int launch_row_grad(const float* A, const float* logits, const float* loss_rows,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int P, HeadParams hp,
                     float dloss_scale, const float* dlogits, const float* dA, float* gsim, float* GA,
                     cudaStream_t st) {
+    ProfScope _ps(kProfRowGrad, st);
     row_grad_kernel<<<N_v, kRowGradThreads, 0, st>>>(A, logits, loss_rows, pos_idx, col_offset, N_a,
                                                      P, hp, dloss_scale, dlogits, dA, gsim, GA);
     AVT_LAUNCH_CHECK();
@@ -323,6 +325,7 @@ int launch_bwd_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, const float* gsim,
                     const float* GA, float* dvh, float* dah, cudaStream_t st) {
+    ProfScope _ps(kProfBwdG, st);
     const int PS = P + 1;
     size_t smem = ((size_t)C * kKT + (size_t)kKT * PS + (size_t)kBwdChunk * PS + P +
                    2 * (kSimThreads / 32) * kKT + 2 * kKT) * sizeof(float);
@@ -381,6 +384,7 @@ dv_finish_kernel(const float* __restrict__ v, const float* __restrict__ rnorm_v,
 
 int launch_dv_finish(const float* v, const float* rnorm_v, int N_v, int C, int P, float* dv,
                      cudaStream_t st) {
+    ProfScope _ps(kProfDvFinish, st);
     dim3 grid(2, N_v);
     dv_finish_kernel<<<grid, kFinThreads, 0, st>>>(v, rnorm_v, C, P, dv);
     AVT_LAUNCH_CHECK();

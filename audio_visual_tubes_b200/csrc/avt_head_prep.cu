@@ -147,6 +147,7 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
 int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_idx, int col_offset,
                        int N_v, int N_a, int C, int P, float* rnorm_v, float* A, float* msum,
                        __nv_bfloat16* vt_bf16, HeadScratch* scratch, cudaStream_t st) {
+    ProfScope _ps(kProfPrep, st);
     dim3 grid(2, N_v);
     size_t smem = (size_t)(C + 3 * kPrepGroups * 128) * sizeof(float);
     if (vt_bf16)
@@ -269,6 +270,7 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
 int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int P, HeadParams hp,
                        float* Pos, float* Neg, float* weighted_A, float* logits,
                        float* loss_rows, float* loss_sum, HeadScratch* scratch, cudaStream_t st) {
+    ProfScope _ps(kProfFinish, st);
     finish_rows_kernel<<<N_v, kRowThreads, 0, st>>>(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A,
                                                     logits, loss_rows, loss_sum, scratch);
     AVT_LAUNCH_CHECK();

@@ -183,6 +183,7 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
                     int col_offset, int N_v, int N_a, int C, int P, HeadParams hp, float* logits,
                     float* sim, float* den, cudaStream_t st) {
+    ProfScope _ps(kProfSim, st);
     AVT_REQUIRE(C % kBK == 0 && C <= kMaxKC * kBK, "bf16 head: C=%d must be a multiple of 64, <= 512", C);
     AVT_REQUIRE(P % 4 == 0 && P <= kBN, "bf16 head: P=%d must be a multiple of 4, <= 208", P);
     const int n_mt = (N_a + kBM - 1) / kBM;

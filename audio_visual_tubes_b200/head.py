@@ -208,3 +208,40 @@ def hardway_loss(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=
     if v.dim() == 4:
         v = v.flatten(2)
     return _HardWayLoss.apply(v, a, cfg, pos_idx, col_offset, float(divisor or v.shape[0]))
+
+
+def hardway_value_and_grad(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0,
+                           divisor=None, want_grad=True):
+    """One training step of the head without autograd bookkeeping: returns
+    ``(loss [1] device tensor, dv [N_v,C,P], da [N_a,C])`` for
+    ``loss = sum_n CE(logits[n], 0) / divisor`` (divisor defaults to N_v: the reference's
+    ``CrossEntropyLoss`` mean, train_hardway_1frame.py:130-133).  Everything is enqueued on the
+    current stream; nothing synchronises."""
+    _lib.require_cuda(v, a)
+    if v.dim() == 4:
+        v = v.flatten(2)
+    v = v.contiguous().float()
+    divisor = float(divisor or v.shape[0])
+    a_hat, rn_a = audio_normalize(a)
+    out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=want_grad)
+    loss = out["loss_sum"] / divisor
+    if not want_grad:
+        return loss, None, None
+    dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 1.0 / divisor, None, None, col_offset)
+    da = audio_normalize_backward(a_hat, rn_a, d_ahat)
+    return loss, dv, da
+
+
+def hardway_value_and_grad_host(v_host, a_host, cfg: HeadConfig = HeadConfig(), device=None,
+                                want_grad=True):
+    """The same step for HOST buffers (pinned memory recommended): copies the features to
+    the device, runs the step, and returns ``(loss as a Python float, dv, da)`` with the
+    gradients left on the device for the backbone's backward.  This is the end-to-end call
+    bench.py times (H2D of v and a, D2H of the loss)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("libavtubes runs on the GPU only (there is no CPU fallback)")
+    dev = torch.device(device or "cuda")
+    v = v_host.to(dev, non_blocking=True)
+    a = a_host.to(dev, non_blocking=True)
+    loss, dv, da = hardway_value_and_grad(v, a, cfg, want_grad=want_grad)
+    return float(loss.cpu()[0]), dv, da

@@ -49,6 +49,27 @@ const char* avt_last_error(void);
 /* 1 if the current device can run the library (compute capability 10.x), else 0 */
 int         avt_device_ok(void);
 
+/* ---- measurement aids (used by bench.py; process-global, single caller) ------------------
+ * avt_launch_count: kernels this library has launched since it was loaded.
+ * avt_profile_enable(1) makes every entry point bracket its stages with CUDA events on the
+ * stream it launches on; avt_profile_read(slot) synchronises those events and returns their
+ * summed duration and the number of intervals since the last avt_profile_enable call.
+ * Slots: 0 visual prep, 1 similarity (forward contraction + pooling), 2 row finish,
+ * 3 row gradients, 4 backward cell-gradient contraction, 5 backward dv contraction,
+ * 6 backward d_ahat contraction, 7 normalise Jacobian, 8 evaluation. */
+#define AVT_PROF_PREP      0
+#define AVT_PROF_SIM       1
+#define AVT_PROF_FINISH    2
+#define AVT_PROF_ROWGRAD   3
+#define AVT_PROF_BWD_G     4
+#define AVT_PROF_BWD_DV    5
+#define AVT_PROF_BWD_DA    6
+#define AVT_PROF_DVFINISH  7
+#define AVT_PROF_EVAL      8
+long long avt_launch_count(void);
+int       avt_profile_enable(int on);
+int       avt_profile_read(int slot, double* total_ms, int* intervals);
+
 /* ---- audio embedding normalisation ---------------------------------------------
  * F.normalize(aud, dim=1)                        model.py:122 (tube :31)
  * a_hat[k,:] = a[k,:] / max(||a[k,:]||, 1e-12);  rnorm_a[k] = 1 / max(||a[k,:]||, 1e-12) */
