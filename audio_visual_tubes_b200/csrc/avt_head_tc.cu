@@ -34,11 +34,19 @@ constexpr int kAccCols = 256;
 constexpr int kTmemCols = 512;
 constexpr size_t kTcSmemBytes = 1024 + (size_t)kMaxKC * kABytes + (size_t)kStagesB * kBBytes + 256;
 
+// kGrad = false: forward (writes sim / den / logits).
+// kGrad = true : backward stage 1.  The same contraction is recomputed and the epilogue turns
+//   every cell into its gradient  G = gsim/den * w (1 + (S - sim)(1 - w)/tau)  (+ GA on the
+//   positive column), stored as bf16 in G[n*P + p][k] (row pitch n_a_pad) --
+//   the K-major A operand of the dv contraction and the MN-major A operand of the d_ahat one.
+template <bool kGrad>
 __global__ void __launch_bounds__(kTcThreads, 1)
 sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 const int32_t* __restrict__ pos_idx, int col_offset, int N_v, int N_a, int n_mt,
                 int groups, int KC, int P, HeadParams hp, int L, float* __restrict__ logits,
-                float* __restrict__ sim, float* __restrict__ den) {
+                float* __restrict__ sim, float* __restrict__ den,
+                const float* __restrict__ gsim, const float* __restrict__ GA,
+                __nv_bfloat16* __restrict__ G, int n_a_pad) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sA = base;
@@ -124,12 +132,21 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         const int q = warp & 3;                          // TMEM lane quarter this warp may touch
         const int row = q * 32 + lane;
         const float c1 = -kLog2e / hp.tau, c0 = hp.eps * kLog2e / hp.tau;
-        const float itemp = 1.0f / hp.temp;
+        const float itemp = 1.0f / hp.temp, itau = 1.0f / hp.tau;
         uint32_t tile = 0;
         for (int mt = mt0; mt < n_mt; mt += mt_step) {
             const int k = mt * kBM + row;
             for (int n = g; n < N_v; n += groups, ++tile) {
                 const uint32_t buf = tile & 1u, use = tile >> 1;
+                const int pos = pos_idx ? pos_idx[n] : col_offset + n;
+                float sm = 0.f, coef = 0.f;
+                if (kGrad && k < N_a) {
+                    sm = sim[(size_t)n * N_a + k];
+                    coef = gsim[(size_t)n * N_a + k] / den[(size_t)n * N_a + k];
+                }
+                const bool is_pos = kGrad && (k == pos);
+                const float* ga = GA + (size_t)n * P;
+                __nv_bfloat16* gout = G + (size_t)n * P * n_a_pad + k;
                 mbar_wait(&tmem_full[buf], use & 1u);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccCols;
@@ -143,8 +160,15 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     for (int i = 0; i < 32; ++i) {
                         const float s = __uint_as_float(r[i]);
                         const float w = fast_rcp(1.0f + fast_ex2(fmaf(s, c1, c0)));
-                        dn += w;
-                        num = fmaf(w, s, num);
+                        if (kGrad) {
+                            const float x = fmaf(-w, itau, itau);            // (1 - w) / tau
+                            float gv = coef * w * fmaf(s - sm, x, 1.0f);
+                            if (is_pos) gv += ga[c + i];
+                            gout[(size_t)(c + i) * n_a_pad] = __float2bfloat16_rn(gv);
+                        } else {
+                            dn += w;
+                            num = fmaf(w, s, num);
+                        }
                     }
                 }
                 for (; c < P; c += 4) {
@@ -155,19 +179,25 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     for (int i = 0; i < 4; ++i) {
                         const float s = __uint_as_float(r[i]);
                         const float w = fast_rcp(1.0f + fast_ex2(fmaf(s, c1, c0)));
-                        dn += w;
-                        num = fmaf(w, s, num);
+                        if (kGrad) {
+                            const float x = fmaf(-w, itau, itau);
+                            float gv = coef * w * fmaf(s - sm, x, 1.0f);
+                            if (is_pos) gv += ga[c + i];
+                            gout[(size_t)(c + i) * n_a_pad] = __float2bfloat16_rn(gv);
+                        } else {
+                            dn += w;
+                            num = fmaf(w, s, num);
+                        }
                     }
                 }
                 tc_fence_before();
                 mbar_arrive(&tmem_empty[buf]);           // accumulator may be overwritten
-                if (k < N_a) {
-                    const int pos = pos_idx ? pos_idx[n] : col_offset + n;
-                    const float sm = num / dn;
+                if (!kGrad && k < N_a) {
+                    const float smv = num / dn;
                     const float m = (k == pos) ? (1.0f - hp.mask_scale) : 1.0f;
-                    sim[(size_t)n * N_a + k] = sm;
+                    sim[(size_t)n * N_a + k] = smv;
                     den[(size_t)n * N_a + k] = dn;
-                    logits[(size_t)n * L + 1 + k] = sm * m * itemp;
+                    logits[(size_t)n * L + 1 + k] = smv * m * itemp;
                 }
             }
         }
@@ -180,10 +210,10 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }
 }
 
-int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
-                    int col_offset, int N_v, int N_a, int C, int P, HeadParams hp, float* logits,
-                    float* sim, float* den, cudaStream_t st) {
-    ProfScope _ps(kProfSim, st);
+static int launch_sim_tc(bool grad, const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
+                         const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
+                         HeadParams hp, float* logits, float* sim, float* den, const float* gsim,
+                         const float* GA, __nv_bfloat16* G, int n_a_pad, cudaStream_t st) {
     AVT_REQUIRE(C % kBK == 0 && C <= kMaxKC * kBK, "bf16 head: C=%d must be a multiple of 64, <= 512", C);
     AVT_REQUIRE(P % 4 == 0 && P <= kBN, "bf16 head: P=%d must be a multiple of 4, <= 208", P);
     const int n_mt = (N_a + kBM - 1) / kBM;
@@ -202,28 +232,39 @@ int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const in
     if (groups < 1) groups = 1;
     const int grid = groups * mt_par;
     const int L = N_a + 1 + (hp.use_neg ? 1 : 0);
-    AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)kTcSmemBytes));
-    sim_bf16_kernel<<<grid, kTcThreads, kTcSmemBytes, st>>>(map_a, map_b, pos_idx, col_offset, N_v, N_a,
-                                                           n_mt, groups, C / kBK, P, hp, L, logits, sim,
-                                                           den);
+    if (grad) {
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)kTcSmemBytes));
+        sim_bf16_kernel<true><<<grid, kTcThreads, kTcSmemBytes, st>>>(
+            map_a, map_b, pos_idx, col_offset, N_v, N_a, n_mt, groups, C / kBK, P, hp, L, logits, sim, den,
+            gsim, GA, G, n_a_pad);
+    } else {
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)kTcSmemBytes));
+        sim_bf16_kernel<false><<<grid, kTcThreads, kTcSmemBytes, st>>>(
+            map_a, map_b, pos_idx, col_offset, N_v, N_a, n_mt, groups, C / kBK, P, hp, L, logits, sim, den,
+            nullptr, nullptr, nullptr, 0);
+    }
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
 
-// Backward in bf16 mode: until the tensor-core gradient kernels land the cell gradients are
-// recomputed on the CUDA cores in fp32 (same kernels as AVT_PRECISION_FP32).
-int launch_bwd_bf16(const float* v, const __nv_bfloat16*, const __nv_bfloat16*, __nv_bfloat16*,
-                    __nv_bfloat16*, const float* a_hat, const float* rnorm_v, const int32_t* pos_idx,
-                    int col_offset, int N_v, int N_a, int, int C, int P, HeadParams hp, const float* sim,
-                    const float* den, const float* gsim, const float* GA, float* dv, float* d_ahat,
-                    cudaStream_t st) {
-    AVT_CHECK_CUDA(cudaMemsetAsync(dv, 0, (size_t)N_v * C * P * sizeof(float), st));
-    (void)sim; (void)den;
-    int rc = launch_bwd_fp32(v, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a, C, P, hp, gsim, GA, dv,
-                             d_ahat, st);
-    if (rc != AVT_OK) return rc;
-    return launch_dv_finish(v, rnorm_v, N_v, C, P, dv, st);
+int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
+                    int col_offset, int N_v, int N_a, int C, int P, HeadParams hp, float* logits,
+                    float* sim, float* den, cudaStream_t st) {
+    ProfScope _ps(kProfSim, st);
+    return launch_sim_tc(false, vt, a_bf, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den,
+                         nullptr, nullptr, nullptr, 0, st);
+}
+
+// backward stage 1: cell gradients G (bf16, [N_v*P][n_a_pad])
+int launch_grad_cells_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
+                           int col_offset, int N_v, int N_a, int n_a_pad, int C, int P, HeadParams hp,
+                           const float* sim, const float* den, const float* gsim, const float* GA,
+                           __nv_bfloat16* G, cudaStream_t st) {
+    ProfScope _ps(kProfBwdG, st);
+    return launch_sim_tc(true, vt, a_bf, pos_idx, col_offset, N_v, N_a, C, P, hp, nullptr,
+                         const_cast<float*>(sim), const_cast<float*>(den), gsim, GA, G, n_a_pad, st);
 }
 
 }  // namespace avt

@@ -1,0 +1,385 @@
+// AVT_PRECISION_BF16 backward on the tensor cores.  Three stages:
+//
+//   1. sim_bf16_kernel<true> (avt_head_tc.cu) recomputes S tile by tile and stores the cell
+//      gradients G[n*P + p][k] as bf16 (row pitch n_a_pad).
+//   2. bwd_dv_kernel:  dv_hat[np, c] = sum_k G[np, k] a_hat[k, c]   (M = 128 rows of np,
+//      N = C in two halves of <= 256, K = n_a_pad), epilogue = the F.normalize Jacobian
+//      dv = rn (dv_hat - v_hat <v_hat, dv_hat>) (model.py:117) written straight into the
+//      NCHW fp32 gradient.  Both operands K-major (G rows, a_hat^T rows).
+//   3. bwd_da_kernel:  d_ahat[k, c] = sum_np G[np, k] v_hat[np, c]  (M = 128 audio rows,
+//      N = C, K = N_v*P split over the grid).  Both operands are MN-major views of the
+//      same row-major buffers stage 1 and the forward left behind, so nothing is
+//      transposed in memory; partial sums are reduced with red.global.add.
+//
+// All three are TMA-fed tcgen05 kernels with the accumulators in tensor memory.
+#include "avt_common.cuh"
+#include "avt_tc.cuh"
+
+namespace avt {
+using namespace tc;
+
+// ------------------------------------------------------------------ a_hat^T (bf16)
+__global__ void transpose_audio_kernel(const __nv_bfloat16* __restrict__ a_bf, int n_a_pad, int C,
+                                       __nv_bfloat16* __restrict__ at_bf) {
+    __shared__ __nv_bfloat16 tile[32][33];
+    const int k0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y)
+        tile[r][threadIdx.x] = a_bf[(size_t)(k0 + r) * C + c0 + threadIdx.x];
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y)
+        at_bf[(size_t)(c0 + r) * n_a_pad + k0 + threadIdx.x] = tile[threadIdx.x][r];
+}
+
+// ------------------------------------------------------------------ stage 2: dv
+constexpr int kDvThreads = 320;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2..9 epilogue
+constexpr int kDvBM = 128;
+constexpr int kDvBK = 64;
+constexpr int kDvStages = 4;
+constexpr int kDvABytes = kDvBM * kDvBK * 2;          // 16384
+constexpr int kDvBBytes = 256 * kDvBK * 2;            // 32768 (one half of C)
+constexpr int kDvStageBytes = kDvABytes + kDvBBytes;
+constexpr size_t kDvSmemBytes = 1024 + (size_t)kDvStages * kDvStageBytes + 256 + 2 * 2 * kDvBM * 4;
+
+__device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+
+__global__ void __launch_bounds__(kDvThreads, 1)
+bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_at,
+              const float* __restrict__ v, const __nv_bfloat16* __restrict__ vt,
+              const float* __restrict__ rnorm_v, float* __restrict__ dv, int n_rows, int n_tiles,
+              int KC, int C, int P) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* stages = base;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stages + (size_t)kDvStages * kDvStageBytes);
+    uint64_t* full_b = bars;                             // [kDvStages]
+    uint64_t* empty_b = bars + kDvStages;                // [kDvStages]
+    uint64_t* tmem_full = bars + 2 * kDvStages;          // [2] one per half of C
+    uint64_t* tmem_empty = tmem_full + 2;                // [2]
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    float* t_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][2][128]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nh = C > 256 ? 2 : 1;
+    const int hN0 = C > 256 ? 256 : C, hN1 = C - hN0;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&map_g);
+        prefetch_tmap(&map_at);
+        for (int i = 0; i < kDvStages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 256); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_holder, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+
+    if (warp == 0) {
+        if (lane == 0) {                                 // ---------------- TMA producer
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int h = 0; h < nh; ++h) {
+                    for (int kc = 0; kc < KC; ++kc) {
+                        mbar_wait(&empty_b[stage], phase ^ 1);
+                        mbar_arrive_expect_tx(&full_b[stage], (uint32_t)kDvStageBytes);
+                        uint8_t* sA = stages + (size_t)stage * kDvStageBytes;
+                        tma_load_2d(sA, &map_g, &full_b[stage], kc * kDvBK, tile * kDvBM);
+                        tma_load_2d(sA + kDvABytes, &map_at, &full_b[stage], kc * kDvBK, h * 256);
+                        if (++stage == kDvStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {                                 // ---------------- MMA issuer
+            int stage = 0; uint32_t phase = 0, it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+                for (int h = 0; h < nh; ++h) {
+                    const uint32_t idesc = make_idesc_bf16(kDvBM, h ? hN1 : hN0, 0, 0);
+                    mbar_wait(&tmem_empty[h], (it & 1u) ^ 1u);
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + (uint32_t)h * 256u;
+                    for (int kc = 0; kc < KC; ++kc) {
+                        mbar_wait(&full_b[stage], phase);
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_u32(stages + (size_t)stage * kDvStageBytes);
+                        const uint32_t b_addr = a_addr + kDvABytes;
+#pragma unroll
+                        for (int k = 0; k < kDvBK / 16; ++k) {
+                            const uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
+                            const uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
+                            umma_bf16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                        }
+                        umma_commit(&empty_b[stage]);
+                        if (++stage == kDvStages) { stage = 0; phase ^= 1; }
+                    }
+                    umma_commit(&tmem_full[h]);
+                }
+            }
+        }
+    } else {                                             // ---------------- epilogue warps 2..9
+        const int q = warp & 3;                          // TMEM lane quarter
+        const int grp = (warp - 2) >> 2;                 // column group inside a half
+        const int r_in = q * 32 + lane;
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+            const int row = tile * kDvBM + r_in;
+            const bool valid = row < n_rows;
+            const int n = valid ? row / P : 0;
+            const int p = valid ? row - n * P : 0;
+            const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+            // pass 1: t = <v_hat[row, :], dv_hat[row, :]> over this thread's columns
+            float t = 0.f;
+            for (int h = 0; h < nh; ++h) {
+                const int hN = h ? hN1 : hN0, cw = hN >> 1;
+                mbar_wait(&tmem_full[h], it & 1u);
+                tc_fence_after();
+                const uint4* vrow = reinterpret_cast<const uint4*>(vt + (size_t)row * C + h * 256 + grp * cw);
+                for (int c = 0; c < cw; c += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(lane_addr + (uint32_t)(h * 256 + grp * cw + c), r);
+                    uint4 x[4];
+                    if (valid) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) x[j] = __ldg(vrow + (c >> 3) + j);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) x[j] = make_uint4(0, 0, 0, 0);
+                    }
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t w[4] = {x[j].x, x[j].y, x[j].z, x[j].w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            t = fmaf(bf_lo(w[e]), __uint_as_float(r[8 * j + 2 * e]), t);
+                            t = fmaf(bf_hi(w[e]), __uint_as_float(r[8 * j + 2 * e + 1]), t);
+                        }
+                    }
+                }
+            }
+            float* tp = t_part + (it & 1u) * 2 * kDvBM;
+            tp[grp * kDvBM + r_in] = t;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            t = tp[r_in] + tp[kDvBM + r_in];
+            // pass 2: dv = rn * (dv_hat - v_hat * t), NCHW fp32
+            const float rn = valid ? rnorm_v[row] : 0.f;
+            const float rt = rn * t;
+            for (int h = 0; h < nh; ++h) {
+                const int hN = h ? hN1 : hN0, cw = hN >> 1;
+                const int cbase = h * 256 + grp * cw;
+                const size_t off0 = ((size_t)n * C + cbase) * P + p;
+                for (int c = 0; c < cw; c += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(lane_addr + (uint32_t)(cbase + c), r);
+                    float xv[32];
+                    if (valid) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) xv[i] = __ldg(v + off0 + (size_t)(c + i) * P);
+                    }
+                    tmem_ld_wait();
+                    if (valid) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            dv[off0 + (size_t)(c + i) * P] = rn * fmaf(-xv[i], rt, __uint_as_float(r[i]));
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[h]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ------------------------------------------------------------------ stage 3: d_ahat
+constexpr int kDaThreads = 192;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2..5 epilogue
+constexpr int kDaBM = 128;
+constexpr int kDaBK = 32;                // rows of np per stage
+constexpr int kDaStages = 4;
+constexpr int kDaBoxBytes = kDaBK * 128; // one [32 rows][64 elements] box
+constexpr int kDaABytes = 2 * kDaBoxBytes;            // 128 audio columns
+constexpr int kDaMaxStageBytes = kDaABytes + 8 * kDaBoxBytes;   // C <= 512
+constexpr size_t kDaSmemBytes = 1024 + (size_t)kDaStages * kDaMaxStageBytes + 256;
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(kDaThreads, 1)
+bwd_da_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_vt,
+              float* __restrict__ d_ahat, int N_a, int n_mt, int splits, int n_chunks, int C) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* stages = base;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stages + (size_t)kDaStages * kDaMaxStageBytes);
+    uint64_t* full_b = bars;
+    uint64_t* empty_b = bars + kDaStages;
+    uint64_t* tmem_full = bars + 2 * kDaStages;
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int mt = blockIdx.x % n_mt, split = blockIdx.x / n_mt;
+    const int ch0 = (int)((long long)split * n_chunks / splits);
+    const int ch1 = (int)((long long)(split + 1) * n_chunks / splits);
+    const int cboxes = C >> 6;
+    const uint32_t stage_bytes = (uint32_t)(kDaABytes + cboxes * kDaBoxBytes);
+    const int nh = C > 256 ? 2 : 1;
+    const int hN0 = C > 256 ? 256 : C, hN1 = C - hN0;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&map_g);
+        prefetch_tmap(&map_vt);
+        for (int i = 0; i < kDaStages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_holder, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+
+    if (warp == 0) {
+        if (lane == 0) {                                 // ---------------- TMA producer
+            int stage = 0; uint32_t phase = 0;
+            for (int ch = ch0; ch < ch1; ++ch) {
+                mbar_wait(&empty_b[stage], phase ^ 1);
+                mbar_arrive_expect_tx(&full_b[stage], stage_bytes);
+                uint8_t* sA = stages + (size_t)stage * kDaMaxStageBytes;
+                uint8_t* sB = sA + kDaABytes;
+                for (int j = 0; j < 2; ++j)
+                    tma_load_2d(sA + j * kDaBoxBytes, &map_g, &full_b[stage], mt * kDaBM + j * 64, ch * kDaBK);
+                for (int j = 0; j < cboxes; ++j)
+                    tma_load_2d(sB + j * kDaBoxBytes, &map_vt, &full_b[stage], j * 64, ch * kDaBK);
+                if (++stage == kDaStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {                                 // ---------------- MMA issuer
+            int stage = 0; uint32_t phase = 0;
+            for (int ch = ch0; ch < ch1; ++ch) {
+                mbar_wait(&full_b[stage], phase);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(stages + (size_t)stage * kDaMaxStageBytes);
+                const uint32_t b_addr = a_addr + kDaABytes;
+#pragma unroll
+                for (int k = 0; k < kDaBK / 16; ++k) {
+                    // MN-major, 128-byte swizzle: 16 K rows = 2 groups of 8 rows (SBO 1024 B);
+                    // consecutive 64-element MN blocks are one box apart (LBO)
+                    const uint64_t ad = make_smem_desc(a_addr + k * 2048, kDaBoxBytes, 1024);
+                    for (int h = 0; h < nh; ++h) {
+                        const uint32_t idesc = make_idesc_bf16(kDaBM, h ? hN1 : hN0, 1, 1);
+                        const uint64_t bd = make_smem_desc(b_addr + h * 4 * kDaBoxBytes + k * 2048, kDaBoxBytes, 1024);
+                        umma_bf16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc,
+                                     (uint32_t)((ch != ch0) || (k != 0)));
+                    }
+                }
+                umma_commit(&empty_b[stage]);
+                if (++stage == kDaStages) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(tmem_full);
+        }
+    } else {                                             // ---------------- epilogue warps 2..5
+        const int q = warp & 3;
+        const int k = mt * kDaBM + q * 32 + lane;
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+        for (int c = 0; c < C; c += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(lane_addr + (uint32_t)c, r);
+            tmem_ld_wait();
+            if (k < N_a) {
+                float* o = d_ahat + (size_t)k * C + c;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                    red_add_v4(o + i, __uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                               __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ------------------------------------------------------------------ launch sequence
+int launch_grad_cells_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
+                           int col_offset, int N_v, int N_a, int n_a_pad, int C, int P, HeadParams hp,
+                           const float* sim, const float* den, const float* gsim, const float* GA,
+                           __nv_bfloat16* G, cudaStream_t st);
+
+int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
+                    __nv_bfloat16* at_bf, __nv_bfloat16* g_bf, const float* a_hat, const float* rnorm_v,
+                    const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C, int P,
+                    HeadParams hp, const float* sim, const float* den, const float* gsim,
+                    const float* GA, float* dv, float* d_ahat, cudaStream_t st) {
+    (void)a_hat;
+    AVT_REQUIRE(C % 64 == 0 && C <= 512, "bf16 backward: C=%d must be a multiple of 64, <= 512", C);
+    const int n_rows = N_v * P;
+    int dev = 0, sms = 148;
+    AVT_CHECK_CUDA(cudaGetDevice(&dev));
+    AVT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+
+    // stage 1: cell gradients
+    int rc = launch_grad_cells_bf16(vt, a_bf, pos_idx, col_offset, N_v, N_a, n_a_pad, C, P, hp, sim, den,
+                                    gsim, GA, g_bf, st);
+    if (rc != AVT_OK) return rc;
+    {
+        dim3 grid(n_a_pad / 32, C / 32), block(32, 8);
+        transpose_audio_kernel<<<grid, block, 0, st>>>(a_bf, n_a_pad, C, at_bf);
+        AVT_LAUNCH_CHECK();
+    }
+    // stage 2: dv
+    {
+        ProfScope _ps(kProfBwdDv, st);
+        CUtensorMap map_g, map_at;
+        if (!make_tmap_bf16_2d(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, kDvBM) ||
+            !make_tmap_bf16_2d(&map_at, at_bf, (uint64_t)C, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, 256)) {
+            set_error("bf16 backward: cuTensorMapEncodeTiled failed (dv)");
+            return AVT_ERR_CUDA;
+        }
+        const int n_tiles = (n_rows + kDvBM - 1) / kDvBM;
+        const int grid = n_tiles < sms ? n_tiles : sms;
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)kDvSmemBytes));
+        bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st>>>(map_g, map_at, v, vt, rnorm_v, dv, n_rows,
+                                                             n_tiles, n_a_pad / kDvBK, C, P);
+        AVT_LAUNCH_CHECK();
+    }
+    // stage 3: d_ahat (zeroed by the caller)
+    {
+        ProfScope _ps(kProfBwdDa, st);
+        CUtensorMap map_g, map_vt;
+        if (!make_tmap_bf16_2d(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, 64, kDaBK) ||
+            !make_tmap_bf16_2d(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, 64, kDaBK)) {
+            set_error("bf16 backward: cuTensorMapEncodeTiled failed (d_ahat)");
+            return AVT_ERR_CUDA;
+        }
+        const int n_mt = n_a_pad / kDaBM;
+        const int n_chunks = (n_rows + kDaBK - 1) / kDaBK;
+        int splits = sms / n_mt;
+        if (splits < 1) splits = 1;
+        if (splits > n_chunks) splits = n_chunks;
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)kDaSmemBytes));
+        bwd_da_kernel<<<n_mt * splits, kDaThreads, kDaSmemBytes, st>>>(map_g, map_vt, d_ahat, N_a, n_mt,
+                                                                      splits, n_chunks, C);
+        AVT_LAUNCH_CHECK();
+    }
+    return AVT_OK;
+}
+
+}  // namespace avt
