@@ -58,88 +58,103 @@ int launch_audio_to_bf16(const float* a_hat, int N_a, int N_a_pad, int C, __nv_b
 
 // ------------------------------------------------------------------ visual prep pass
 // model.py:117 (norm over C per position), :124 (positive map), :150 (mean_c of the
-// normalised map).  grid (2, N_v): each block owns one half of the positions of one
-// image; 4 channel groups x 128 lanes; every thread streams 16 channels per step.
-// With kWriteBf16 a second sweep emits v_hat = v * rnorm as bf16, transposed to [n][p][c].
+// normalised map) and, for the tensor-core path, v_hat as bf16 K-major [n][p][c].
+// ONE read of v: a block owns 32 positions of one image, its 16 warps own C/16 channels
+// each, and every thread keeps its <= 32 values in registers between the reduction over
+// the channels and the normalised write-out (the earlier two-sweep version re-read v from
+// DRAM: ncu showed 750 MB of reads for a 411 MB input).  Loads are 128-byte rows of
+// consecutive positions; stores are 64 contiguous bytes per thread.
 constexpr int kPrepThreads = 512;
-constexpr int kPrepGroups = 4;
+constexpr int kPrepWarps = 16;
+constexpr int kPrepMaxCpw = 32;                  // channels per warp, C <= 512
 
 template <bool kWriteBf16>
-__global__ void __launch_bounds__(kPrepThreads)
+__global__ void __launch_bounds__(kPrepThreads, 2)
 prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
                    const int32_t* __restrict__ pos_idx, int col_offset, int N_a, int C, int P,
                    float* __restrict__ rnorm_v, float* __restrict__ A, float* __restrict__ msum,
                    __nv_bfloat16* __restrict__ vt, HeadScratch* scratch) {
     extern __shared__ float smem[];
     float* s_a = smem;                       // [C]  positive audio row
-    float* s_red = smem + C;                 // [3][kPrepGroups][128]
+    float* s_red = smem + C;                 // [3][kPrepWarps][32]
     const int n = blockIdx.y;
-    const int PT = (P + 1) / 2;
-    const int lane = threadIdx.x & 127;
-    const int g = threadIdx.x >> 7;
-    const int p = blockIdx.x * PT + lane;
-    const bool active = (lane < PT) && (p < P);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int p = blockIdx.x * 32 + lane;
+    const bool active = p < P;
+    const int cpw = C / kPrepWarps;          // channels of this warp: [w*cpw, (w+1)*cpw)
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) scratch->rows_done = 0u;
 
-    int pos = pos_idx ? pos_idx[n] : col_offset + n;
+    const int pos = pos_idx ? pos_idx[n] : col_offset + n;
     const bool has_pos = (pos >= 0 && pos < N_a);
     for (int c = threadIdx.x; c < C; c += kPrepThreads)
         s_a[c] = has_pos ? a_hat[(size_t)pos * C + c] : 0.f;
-    __syncthreads();
 
+    float x[kPrepMaxCpw];
+    const float* vp = v + ((size_t)n * C + (size_t)w * cpw) * P + p;
+#pragma unroll
+    for (int i = 0; i < kPrepMaxCpw; ++i)
+        x[i] = (active && i < cpw) ? __ldg(vp + (size_t)i * P) : 0.f;
+    __syncthreads();                         // s_a ready
     float ssq = 0.f, dot = 0.f, sum = 0.f;
-    const float* vp = v + (size_t)n * C * P + p;
-    if (active) {
-        for (int c0 = g * 16; c0 < C; c0 += 16 * kPrepGroups) {
-            float x[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) x[i] = __ldg(vp + (size_t)(c0 + i) * P);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                ssq = fmaf(x[i], x[i], ssq);
-                dot = fmaf(x[i], s_a[c0 + i], dot);
-                sum += x[i];
-            }
+    for (int i = 0; i < kPrepMaxCpw; ++i) {
+        if (i < cpw) {
+            ssq = fmaf(x[i], x[i], ssq);
+            dot = fmaf(x[i], s_a[w * cpw + i], dot);
+            sum += x[i];
         }
     }
-    s_red[(0 * kPrepGroups + g) * 128 + lane] = ssq;
-    s_red[(1 * kPrepGroups + g) * 128 + lane] = dot;
-    s_red[(2 * kPrepGroups + g) * 128 + lane] = sum;
+    s_red[(0 * kPrepWarps + w) * 32 + lane] = ssq;
+    s_red[(1 * kPrepWarps + w) * 32 + lane] = dot;
+    s_red[(2 * kPrepWarps + w) * 32 + lane] = sum;
     __syncthreads();
-    float rn = 0.f;
-    if (active) {
-        float t0 = 0.f, t1 = 0.f, t2 = 0.f;
+    float t0 = 0.f;
 #pragma unroll
-        for (int j = 0; j < kPrepGroups; ++j) {
-            t0 += s_red[(0 * kPrepGroups + j) * 128 + lane];
-            t1 += s_red[(1 * kPrepGroups + j) * 128 + lane];
-            t2 += s_red[(2 * kPrepGroups + j) * 128 + lane];
+    for (int j = 0; j < kPrepWarps; ++j) t0 += s_red[(0 * kPrepWarps + j) * 32 + lane];
+    const float rn = 1.0f / fmaxf(sqrtf(t0), kNormEps);
+    if (w == 0 && active) {
+        float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < kPrepWarps; ++j) {
+            t1 += s_red[(1 * kPrepWarps + j) * 32 + lane];
+            t2 += s_red[(2 * kPrepWarps + j) * 32 + lane];
         }
-        rn = 1.0f / fmaxf(sqrtf(t0), kNormEps);
-        if (g == 0) {
-            size_t o = (size_t)n * P + p;
-            rnorm_v[o] = rn;
-            A[o] = t1 * rn;
-            msum[o] = t2 * rn / (float)C;
-        }
+        const size_t o = (size_t)n * P + p;
+        rnorm_v[o] = rn;
+        A[o] = t1 * rn;
+        msum[o] = t2 * rn / (float)C;
     }
-    if (kWriteBf16 && active) {
-        // second sweep (L2-resident: this block just streamed these lines): the
-        // normalised map as bf16, K-major [n][p][c] for the tensor-core contraction
-        __nv_bfloat16* op = vt + ((size_t)n * P + p) * C;
-        for (int c0 = g * 16; c0 < C; c0 += 16 * kPrepGroups) {
-            float x[16];
+    if (kWriteBf16) {
+        // transpose through shared memory so the K-major rows leave as 512-byte bursts:
+        // tile[p][c] bf16 with a 16-byte pad per row (16-byte accesses stay conflict-free)
+        uint8_t* s_tile = reinterpret_cast<uint8_t*>(s_red + 3 * kPrepWarps * 32);
+        const int pitch = C * 2 + 16;
 #pragma unroll
-            for (int i = 0; i < 16; ++i) x[i] = __ldg(vp + (size_t)(c0 + i) * P) * rn;
-            uint32_t w[8];
+        for (int i = 0; i < kPrepMaxCpw; i += 8) {
+            if (i < cpw) {
+                uint32_t wds[4];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                __nv_bfloat162 h = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
-                w[i] = *reinterpret_cast<uint32_t*>(&h);
+                for (int e = 0; e < 4; ++e) {
+                    __nv_bfloat162 h = __floats2bfloat162_rn(x[i + 2 * e] * rn, x[i + 2 * e + 1] * rn);
+                    wds[e] = *reinterpret_cast<uint32_t*>(&h);
+                }
+                if (cpw % 8 == 0) {
+                    *reinterpret_cast<uint4*>(s_tile + (size_t)lane * pitch + (w * cpw + i) * 2) =
+                        make_uint4(wds[0], wds[1], wds[2], wds[3]);
+                } else {                         // cpw a multiple of 4 only: 8-byte pieces
+                    uint8_t* o = s_tile + (size_t)lane * pitch + (w * cpw + i) * 2;
+                    *reinterpret_cast<uint2*>(o) = make_uint2(wds[0], wds[1]);
+                    if (i + 4 < cpw) *reinterpret_cast<uint2*>(o + 8) = make_uint2(wds[2], wds[3]);
+                }
             }
-            uint4* o = reinterpret_cast<uint4*>(op + c0);
-            o[0] = make_uint4(w[0], w[1], w[2], w[3]);
-            o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+        }
+        __syncthreads();
+        // warp w writes rows w, w+16 of the tile; a lane moves 16 bytes per step
+        const int p0 = blockIdx.x * 32;
+        for (int r = w; r < 32 && p0 + r < P; r += kPrepWarps) {
+            uint8_t* dst = reinterpret_cast<uint8_t*>(vt + ((size_t)n * P + p0 + r) * C);
+            for (int b = lane * 16; b < C * 2; b += 32 * 16)
+                *reinterpret_cast<uint4*>(dst + b) = *reinterpret_cast<const uint4*>(s_tile + (size_t)r * pitch + b);
         }
     }
 }
@@ -148,8 +163,9 @@ int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_id
                        int N_v, int N_a, int C, int P, float* rnorm_v, float* A, float* msum,
                        __nv_bfloat16* vt_bf16, HeadScratch* scratch, cudaStream_t st) {
     ProfScope _ps(kProfPrep, st);
-    dim3 grid(2, N_v);
-    size_t smem = (size_t)(C + 3 * kPrepGroups * 128) * sizeof(float);
+    AVT_REQUIRE(C % 64 == 0 && C <= kPrepWarps * kPrepMaxCpw, "prep: C=%d must be a multiple of 64, <= 512", C);
+    dim3 grid((P + 31) / 32, N_v);
+    size_t smem = (size_t)(C + 3 * kPrepWarps * 32) * sizeof(float) + (vt_bf16 ? (size_t)32 * (C * 2 + 16) : 0);
     if (vt_bf16)
         prep_visual_kernel<true><<<grid, kPrepThreads, smem, st>>>(v, a_hat, pos_idx, col_offset, N_a,
                                                                   C, P, rnorm_v, A, msum, vt_bf16, scratch);

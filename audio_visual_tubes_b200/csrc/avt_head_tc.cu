@@ -22,7 +22,7 @@
 namespace avt {
 using namespace tc;
 
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 320;                         // warp 0 TMA, 1 MMA, 2..9 epilogue
 constexpr int kBM = 128;
 constexpr int kBN = 208;
 constexpr int kBK = 64;
@@ -32,7 +32,69 @@ constexpr int kABytes = kBM * kBK * 2;                  // 16384 per K chunk
 constexpr int kBBytes = kBN * kBK * 2;                  // 26624 per stage
 constexpr int kAccCols = 256;
 constexpr int kTmemCols = 512;
-constexpr size_t kTcSmemBytes = 1024 + (size_t)kMaxKC * kABytes + (size_t)kStagesB * kBBytes + 256;
+constexpr size_t kTcSmemBytes = 1024 + (size_t)kMaxKC * kABytes + (size_t)kStagesB * kBBytes + 256 + 2 * kBM * 8;
+
+// One chunk of N accumulator columns of one TMEM lane.  w = sigma((s - eps)/tau) =
+// 1 / (1 + 2^(s*c1 + c0)).  The fast variant shares one MUFU.RCP between two cells
+// (r = 1/(x0*x1); w0 = r*x1; w1 = r*x0), which needs the exponent clamped so the product
+// cannot overflow; clamped cells only matter when EVERY weight of the (n, k) pair is below
+// 2^-30, and in that case the caller redoes the pair with kExact = true (one RCP per cell,
+// no clamp), so results never depend on the clamp.
+struct CellCtx {
+    float c1, c0, itau;          // sigmoid constants
+    float sm, coef;              // backward: pooled sim and gsim / den of this (n, k)
+};
+constexpr float kExpClamp = 60.0f;
+constexpr float kTinyDen = 9.313225746154785e-10f;      // 2^-30
+
+template <bool kGrad, bool kExact, int N>
+__device__ __forceinline__ void cell_chunk(const uint32_t (&r)[N], const CellCtx& cx, float& num,
+                                           float& dn, __nv_bfloat16* gp, uint32_t pitch) {
+#pragma unroll
+    for (int i = 0; i < N; i += 2) {
+        const float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
+        float w0, w1;
+        if (kExact) {
+            w0 = fast_rcp(1.0f + fast_ex2(fmaf(s0, cx.c1, cx.c0)));
+            w1 = fast_rcp(1.0f + fast_ex2(fmaf(s1, cx.c1, cx.c0)));
+        } else {
+            const float x0 = 1.0f + fast_ex2(fminf(fmaf(s0, cx.c1, cx.c0), kExpClamp));
+            const float x1 = 1.0f + fast_ex2(fminf(fmaf(s1, cx.c1, cx.c0), kExpClamp));
+            const float rr = fast_rcp(x0 * x1);
+            w0 = rr * x1;
+            w1 = rr * x0;
+        }
+        if (kGrad) {
+            const float g0 = (cx.coef * w0) * fmaf(s0 - cx.sm, fmaf(-w0, cx.itau, cx.itau), 1.0f);
+            const float g1 = (cx.coef * w1) * fmaf(s1 - cx.sm, fmaf(-w1, cx.itau, cx.itau), 1.0f);
+            gp[(uint32_t)i * pitch] = __float2bfloat16_rn(g0);
+            gp[(uint32_t)(i + 1) * pitch] = __float2bfloat16_rn(g1);
+        } else {
+            dn += w0 + w1;
+            num = fmaf(w0, s0, num);
+            num = fmaf(w1, s1, num);
+        }
+    }
+}
+
+// all columns [c_begin, c_end) of one TMEM lane (c_end - c_begin a multiple of 4)
+template <bool kGrad, bool kExact>
+__device__ __forceinline__ void cell_sweep(uint32_t taddr, int c_begin, int c_end, const CellCtx& cx,
+                                           float& num, float& dn, __nv_bfloat16* gout, uint32_t pitch) {
+    int c = c_begin;
+    for (; c + 32 <= c_end; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c, r);
+        tmem_ld_wait();
+        cell_chunk<kGrad, kExact, 32>(r, cx, num, dn, gout + (uint32_t)c * pitch, pitch);
+    }
+    for (; c < c_end; c += 4) {
+        uint32_t r[4];
+        tmem_ld_32x4(taddr + c, r);
+        tmem_ld_wait();
+        cell_chunk<kGrad, kExact, 4>(r, cx, num, dn, gout + (uint32_t)c * pitch, pitch);
+    }
+}
 
 // kGrad = false: forward (writes sim / den / logits).
 // kGrad = true : backward stage 1.  The same contraction is recomputed and the epilogue turns
@@ -59,6 +121,7 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint64_t* tmem_full = a_empty + 1;                   // [2]
     uint64_t* tmem_empty = tmem_full + 2;                // [2]
     uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    float2* part = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][kBM]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int mt0 = blockIdx.x / groups, g = blockIdx.x % groups, mt_step = gridDim.x / groups;
@@ -69,7 +132,7 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         for (int i = 0; i < kStagesB; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
         mbar_init(a_full, 1);
         mbar_init(a_empty, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 128); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 256); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_holder, kTmemCols);
@@ -128,8 +191,13 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 umma_commit(a_empty);
             }
         }
-    } else {                                             // ---------------- epilogue warps 2..5
+    } else {                                             // ---------------- epilogue warps 2..9
+        // two warps per TMEM lane quarter (one per scheduler pair): each takes half of the
+        // image's positions, so every SM sub-partition has two warps to hide MUFU / TMEM latency
         const int q = warp & 3;                          // TMEM lane quarter this warp may touch
+        const int half = (warp - 2) >> 2;
+        const int split = ((P >> 1) >> 5) << 5;          // 96 for P = 196
+        const int c_begin = half ? split : 0, c_end = half ? P : split;
         const int row = q * 32 + lane;
         const float c1 = -kLog2e / hp.tau, c0 = hp.eps * kLog2e / hp.tau;
         const float itemp = 1.0f / hp.temp, itau = 1.0f / hp.tau;
@@ -139,60 +207,50 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             for (int n = g; n < N_v; n += groups, ++tile) {
                 const uint32_t buf = tile & 1u, use = tile >> 1;
                 const int pos = pos_idx ? pos_idx[n] : col_offset + n;
-                float sm = 0.f, coef = 0.f;
-                if (kGrad && k < N_a) {
-                    sm = sim[(size_t)n * N_a + k];
-                    coef = gsim[(size_t)n * N_a + k] / den[(size_t)n * N_a + k];
+                CellCtx cx{c1, c0, itau, 0.f, 0.f};
+                bool exact = false;
+                if (kGrad) {
+                    float dnk = 1.0f;
+                    if (k < N_a) {
+                        dnk = den[(size_t)n * N_a + k];
+                        cx.sm = sim[(size_t)n * N_a + k];
+                        cx.coef = gsim[(size_t)n * N_a + k] / dnk;
+                    }
+                    exact = __any_sync(0xffffffffu, dnk < kTinyDen);
                 }
-                const bool is_pos = kGrad && (k == pos);
-                const float* ga = GA + (size_t)n * P;
                 __nv_bfloat16* gout = G + (size_t)n * P * n_a_pad + k;
+                const uint32_t pitch = (uint32_t)n_a_pad;
                 mbar_wait(&tmem_full[buf], use & 1u);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccCols;
                 float num = 0.f, dn = 0.f;
-                int c = 0;
-                for (; c + 32 <= P; c += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(taddr + c, r);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const float s = __uint_as_float(r[i]);
-                        const float w = fast_rcp(1.0f + fast_ex2(fmaf(s, c1, c0)));
-                        if (kGrad) {
-                            const float x = fmaf(-w, itau, itau);            // (1 - w) / tau
-                            float gv = coef * w * fmaf(s - sm, x, 1.0f);
-                            if (is_pos) gv += ga[c + i];
-                            gout[(size_t)(c + i) * n_a_pad] = __float2bfloat16_rn(gv);
-                        } else {
-                            dn += w;
-                            num = fmaf(w, s, num);
-                        }
-                    }
-                }
-                for (; c < P; c += 4) {
-                    uint32_t r[4];
-                    tmem_ld_32x4(taddr + c, r);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float s = __uint_as_float(r[i]);
-                        const float w = fast_rcp(1.0f + fast_ex2(fmaf(s, c1, c0)));
-                        if (kGrad) {
-                            const float x = fmaf(-w, itau, itau);
-                            float gv = coef * w * fmaf(s - sm, x, 1.0f);
-                            if (is_pos) gv += ga[c + i];
-                            gout[(size_t)(c + i) * n_a_pad] = __float2bfloat16_rn(gv);
-                        } else {
-                            dn += w;
-                            num = fmaf(w, s, num);
-                        }
-                    }
-                }
+                // forward: MMA-bound, one RCP per cell is free; backward: MUFU-bound, share RCPs
+                // unless some pair of this warp has every weight below 2^-30 (rare)
+                if (!kGrad || exact) cell_sweep<kGrad, true>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
+                else cell_sweep<kGrad, false>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
                 tc_fence_before();
                 mbar_arrive(&tmem_empty[buf]);           // accumulator may be overwritten
-                if (!kGrad && k < N_a) {
+                if (kGrad) {
+                    // positive column: G[n, pos, p] += GA[n, p] (gradient through A, sim1, sim2).
+                    // The whole warp shares the fix-up of its one positive lane.
+                    const uint32_t m = __ballot_sync(0xffffffffu, k == pos);
+                    if (m) {
+                        __syncwarp();
+                        const int kp = mt * kBM + q * 32 + (__ffs(m) - 1);
+                        __nv_bfloat16* gcol = G + (size_t)n * P * n_a_pad + kp;
+                        for (int pp = c_begin + lane; pp < c_end; pp += 32) {
+                            __nv_bfloat16* a = gcol + (uint32_t)pp * pitch;
+                            *a = __float2bfloat16_rn(__bfloat162float(*a) + GA[(size_t)n * P + pp]);
+                        }
+                    }
+                }
+                if (!kGrad) {                            // combine the two column halves
+                    float2* pp = part + (tile & 1u) * kBM;
+                    if (half) pp[row] = make_float2(num, dn);
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    if (!half) { const float2 o = pp[row]; num += o.x; dn += o.y; }
+                }
+                if (!kGrad && !half && k < N_a) {
                     const float smv = num / dn;
                     const float m = (k == pos) ? (1.0f - hp.mask_scale) : 1.0f;
                     sim[(size_t)n * N_a + k] = smv;

@@ -42,10 +42,16 @@ constexpr size_t kDvSmemBytes = 1024 + (size_t)kDvStages * kDvStageBytes + 256 +
 
 __device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+// 16 consecutive bf16 (32 bytes, 32-byte aligned) through the read-only path in one request
+__device__ __forceinline__ void ld_nc_v8(const __nv_bfloat16* p, uint32_t* r) {
+    asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
 
 __global__ void __launch_bounds__(kDvThreads, 1)
 bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_at,
-              const float* __restrict__ v, const __nv_bfloat16* __restrict__ vt,
+              const __nv_bfloat16* __restrict__ vt,
               const float* __restrict__ rnorm_v, float* __restrict__ dv, int n_rows, int n_tiles,
               int KC, int C, int P) {
     extern __shared__ uint8_t smem_raw[];
@@ -123,40 +129,33 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
         const int q = warp & 3;                          // TMEM lane quarter
         const int grp = (warp - 2) >> 2;                 // column group inside a half
         const int r_in = q * 32 + lane;
+        const uint32_t Pu = (uint32_t)P;
         uint32_t it = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
             const int row = tile * kDvBM + r_in;
             const bool valid = row < n_rows;
-            const int n = valid ? row / P : 0;
-            const int p = valid ? row - n * P : 0;
+            const int rowc = valid ? row : n_rows - 1;   // loads of a ragged last tile stay in bounds
+            const int n = rowc / P;
+            const int p = rowc - n * P;
             const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+            const __nv_bfloat16* vrow = vt + (size_t)rowc * C;
             // pass 1: t = <v_hat[row, :], dv_hat[row, :]> over this thread's columns
             float t = 0.f;
             for (int h = 0; h < nh; ++h) {
                 const int hN = h ? hN1 : hN0, cw = hN >> 1;
+                const int cbase = h * 256 + grp * cw;
                 mbar_wait(&tmem_full[h], it & 1u);
                 tc_fence_after();
-                const uint4* vrow = reinterpret_cast<const uint4*>(vt + (size_t)row * C + h * 256 + grp * cw);
                 for (int c = 0; c < cw; c += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(lane_addr + (uint32_t)(h * 256 + grp * cw + c), r);
-                    uint4 x[4];
-                    if (valid) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) x[j] = __ldg(vrow + (c >> 3) + j);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) x[j] = make_uint4(0, 0, 0, 0);
-                    }
+                    uint32_t r[32], x[16];
+                    tmem_ld_32x32(lane_addr + (uint32_t)(cbase + c), r);
+                    ld_nc_v8(vrow + cbase + c, x);
+                    ld_nc_v8(vrow + cbase + c + 16, x + 8);
                     tmem_ld_wait();
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const uint32_t w[4] = {x[j].x, x[j].y, x[j].z, x[j].w};
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            t = fmaf(bf_lo(w[e]), __uint_as_float(r[8 * j + 2 * e]), t);
-                            t = fmaf(bf_hi(w[e]), __uint_as_float(r[8 * j + 2 * e + 1]), t);
-                        }
+                    for (int e = 0; e < 16; ++e) {
+                        t = fmaf(bf_lo(x[e]), __uint_as_float(r[2 * e]), t);
+                        t = fmaf(bf_hi(x[e]), __uint_as_float(r[2 * e + 1]), t);
                     }
                 }
             }
@@ -164,26 +163,27 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
             tp[grp * kDvBM + r_in] = t;
             asm volatile("bar.sync 1, 256;" ::: "memory");
             t = tp[r_in] + tp[kDvBM + r_in];
-            // pass 2: dv = rn * (dv_hat - v_hat * t), NCHW fp32
-            const float rn = valid ? rnorm_v[row] : 0.f;
+            // pass 2: dv = rn * (dv_hat - v_hat * t), NCHW fp32.  v_hat comes from the bf16
+            // row this thread just read (L1/L2-resident), not from a second sweep over v.
+            const float rn = rnorm_v[rowc];
             const float rt = rn * t;
             for (int h = 0; h < nh; ++h) {
                 const int hN = h ? hN1 : hN0, cw = hN >> 1;
                 const int cbase = h * 256 + grp * cw;
-                const size_t off0 = ((size_t)n * C + cbase) * P + p;
+                float* obase = dv + ((size_t)n * C + cbase) * P + p;
                 for (int c = 0; c < cw; c += 32) {
-                    uint32_t r[32];
+                    uint32_t r[32], x[16];
                     tmem_ld_32x32(lane_addr + (uint32_t)(cbase + c), r);
-                    float xv[32];
-                    if (valid) {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) xv[i] = __ldg(v + off0 + (size_t)(c + i) * P);
-                    }
+                    ld_nc_v8(vrow + cbase + c, x);
+                    ld_nc_v8(vrow + cbase + c + 16, x + 8);
                     tmem_ld_wait();
+                    float* o = obase + (uint32_t)c * Pu;
                     if (valid) {
 #pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            dv[off0 + (size_t)(c + i) * P] = rn * fmaf(-xv[i], rt, __uint_as_float(r[i]));
+                        for (int e = 0; e < 16; ++e) {
+                            o[(uint32_t)(2 * e) * Pu] = fmaf(-bf_lo(x[e]), rt, rn * __uint_as_float(r[2 * e]));
+                            o[(uint32_t)(2 * e + 1) * Pu] = fmaf(-bf_hi(x[e]), rt, rn * __uint_as_float(r[2 * e + 1]));
+                        }
                     }
                 }
                 tc_fence_before();
@@ -326,7 +326,7 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C, int P,
                     HeadParams hp, const float* sim, const float* den, const float* gsim,
                     const float* GA, float* dv, float* d_ahat, cudaStream_t st) {
-    (void)a_hat;
+    (void)a_hat; (void)v;
     AVT_REQUIRE(C % 64 == 0 && C <= 512, "bf16 backward: C=%d must be a multiple of 64, <= 512", C);
     const int n_rows = N_v * P;
     int dev = 0, sms = 148;
@@ -355,7 +355,7 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
         const int grid = n_tiles < sms ? n_tiles : sms;
         AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)kDvSmemBytes));
-        bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st>>>(map_g, map_at, v, vt, rnorm_v, dv, n_rows,
+        bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv, n_rows,
                                                              n_tiles, n_a_pad / kDvBK, C, P);
         AVT_LAUNCH_CHECK();
     }
