@@ -61,6 +61,10 @@ struct ProfScope {
 constexpr float kNormEps = 1e-12f;          // torch.nn.functional.normalize default eps
 constexpr float kLog2e = 1.4426950408889634f;
 
+// audio rows are padded (zero rows) to whole 128-row MMA tiles; above one tile to whole
+// 256-row CTA-pair tiles so the cta_group::2 kernels always see an even tile count
+inline int n_a_padded(int N_a) { return N_a <= 128 ? 128 : (N_a + 255) / 256 * 256; }
+
 struct HeadParams {
     float eps, eps2, tau, temp, mask_scale;
     int trimap, use_neg;

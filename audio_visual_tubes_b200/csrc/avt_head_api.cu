@@ -20,7 +20,7 @@ HeadWorkspace head_workspace_layout(int N_v, int N_a, int C, int P, int precisio
     w.msum = take((size_t)N_v * P * sizeof(float));
     w.gsim = w.ga = w.vt = w.a_bf = w.at_bf = w.g_bf = 0;
     if (precision == AVT_PRECISION_BF16) {
-        const size_t n_a_pad = align_up((size_t)N_a, 128);
+        const size_t n_a_pad = (size_t)n_a_padded(N_a);
         // + one tile of slack rows so the last image's 208-row TMA box stays in bounds
         w.vt = take(((size_t)N_v * P + 64) * C * sizeof(__nv_bfloat16));
         w.a_bf = take(n_a_pad * C * sizeof(__nv_bfloat16));
@@ -99,7 +99,7 @@ extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int
         }
         __nv_bfloat16* vt = reinterpret_cast<__nv_bfloat16*>(ws + w.vt);
         __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
-        const int n_a_pad = (N_a + 127) / 128 * 128;
+        const int n_a_pad = n_a_padded(N_a);
         rc = launch_audio_to_bf16(a_hat, N_a, n_a_pad, C, a_bf, st);
         if (rc != AVT_OK) return rc;
         rc = launch_prep_visual(v, a_hat, pos_idx, col_offset, N_v, N_a, C, P, rnorm_v, A, msum, vt,
@@ -151,7 +151,7 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
         set_error("avt_head_backward: the bf16 tcgen05 path needs an sm_100 device");
         return AVT_ERR_UNSUPPORTED;
     }
-    const int n_a_pad = (N_a + 127) / 128 * 128;
+    const int n_a_pad = n_a_padded(N_a);
     __nv_bfloat16* vt = reinterpret_cast<__nv_bfloat16*>(ws + w.vt);
     __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
     __nv_bfloat16* at_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.at_bf);

@@ -274,7 +274,8 @@ static int launch_sim_tc(bool grad, const __nv_bfloat16* vt, const __nv_bfloat16
                          const float* GA, __nv_bfloat16* G, int n_a_pad, cudaStream_t st) {
     AVT_REQUIRE(C % kBK == 0 && C <= kMaxKC * kBK, "bf16 head: C=%d must be a multiple of 64, <= 512", C);
     AVT_REQUIRE(P % 4 == 0 && P <= kBN, "bf16 head: P=%d must be a multiple of 4, <= 208", P);
-    const int n_mt = (N_a + kBM - 1) / kBM;
+    // backward: every column of G up to n_a_pad must be written (pad columns get zeros)
+    const int n_mt = grad ? n_a_pad / kBM : (N_a + kBM - 1) / kBM;
     CUtensorMap map_a, map_b;
     if (!make_tmap_bf16_2d(&map_a, a_bf, (uint64_t)n_mt * kBM, (uint64_t)C, (uint64_t)C * 2, kBK, kBM) ||
         !make_tmap_bf16_2d(&map_b, vt, (uint64_t)N_v * P, (uint64_t)C, (uint64_t)C * 2, kBK, kBN)) {

@@ -14,6 +14,7 @@
 // All three are TMA-fed tcgen05 kernels with the accumulators in tensor memory.
 #include "avt_common.cuh"
 #include "avt_tc.cuh"
+#include <stdlib.h>
 
 namespace avt {
 using namespace tc;
@@ -315,6 +316,120 @@ bwd_da_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
     }
 }
 
+// ------------------------------------------------------------------ stage 3, CTA pairs
+// Same contraction with tcgen05.mma.cta_group::2: a cluster of two CTAs owns 256 audio rows
+// (M = 256) of one K split.  Per 64-row K chunk each CTA pulls its own 128 columns of G
+// (16 KB) but only HALF of the v_hat chunk (2 x 128 of the 512 channels, 32 KB instead of
+// 64 KB); the hardware reads both halves of B across the pair.  Three TMA instructions per
+// stage per CTA (3-D boxes that land as consecutive MN-major SW128 blocks).
+constexpr int kDa2Threads = 192;
+constexpr int kDa2BK = 64;
+constexpr int kDa2Stages = 4;
+constexpr int kDa2BlockBytes = kDa2BK * 128;          // one [64 rows][64 elements] block, 8 KB
+constexpr int kDa2ABytes = 2 * kDa2BlockBytes;        // this CTA's 128 audio columns
+constexpr int kDa2BHalfBytes = 2 * kDa2BlockBytes;    // this CTA's 128 channels of one N = 256 MMA
+constexpr int kDa2StageBytes = kDa2ABytes + 2 * kDa2BHalfBytes;   // 48 KB
+constexpr size_t kDa2SmemBytes = 1024 + (size_t)kDa2Stages * kDa2StageBytes + 256;
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kDa2Threads, 1)
+bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_vt,
+                   float* __restrict__ d_ahat, int N_a, int n_mt, int splits, int n_chunks, int C) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* stages = base;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stages + (size_t)kDa2Stages * kDa2StageBytes);
+    uint64_t* full_b = bars;                 // used on the leader; both CTAs' TMA bytes land here
+    uint64_t* empty_b = bars + kDa2Stages;   // one per CTA, released by the leader's multicast commit
+    uint64_t* tmem_full = bars + 2 * kDa2Stages;
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int mt = blockIdx.x % n_mt, split = blockIdx.x / n_mt;      // n_mt even: a pair shares `split`
+    const int ch0 = (int)((long long)split * n_chunks / splits);
+    const int ch1 = (int)((long long)(split + 1) * n_chunks / splits);
+    const int nh = C / 256;                  // C is 256 or 512
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&map_g);
+        prefetch_tmap(&map_vt);
+        for (int i = 0; i < kDa2Stages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc2(tmem_holder, 512);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();                          // both CTAs' barriers are initialised before any remote arrive
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+
+    if (warp == 0) {
+        if (lane == 0) {                                 // ---------------- TMA producer (both CTAs)
+            int stage = 0; uint32_t phase = 0;
+            for (int ch = ch0; ch < ch1; ++ch) {
+                mbar_wait(&empty_b[stage], phase ^ 1);
+                if (rank == 0)                           // the leader's barrier counts both CTAs' bytes
+                    mbar_arrive_expect_tx(&full_b[stage], (uint32_t)(2 * (kDa2ABytes + nh * kDa2BHalfBytes)));
+                uint8_t* sA = stages + (size_t)stage * kDa2StageBytes;
+                tma_load_3d_pair(sA, &map_g, &full_b[stage], 0, ch * kDa2BK, mt * 2);
+                for (int h = 0; h < nh; ++h)
+                    tma_load_3d_pair(sA + kDa2ABytes + h * kDa2BHalfBytes, &map_vt, &full_b[stage], 0,
+                                     ch * kDa2BK, h * 4 + (int)rank * 2);
+                if (++stage == kDa2Stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {                    // ---------------- MMA issuer (leader only)
+            const uint32_t idesc = make_idesc_bf16(256, 256, 1, 1);
+            int stage = 0; uint32_t phase = 0;
+            for (int ch = ch0; ch < ch1; ++ch) {
+                mbar_wait(&full_b[stage], phase);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(stages + (size_t)stage * kDa2StageBytes);
+                const uint32_t b_addr = a_addr + kDa2ABytes;
+#pragma unroll
+                for (int k = 0; k < kDa2BK / 16; ++k) {
+                    const uint64_t ad = make_smem_desc(a_addr + k * 2048, kDa2BlockBytes, 1024);
+                    for (int h = 0; h < nh; ++h) {
+                        const uint64_t bd = make_smem_desc(b_addr + h * kDa2BHalfBytes + k * 2048, kDa2BlockBytes, 1024);
+                        umma2_bf16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc,
+                                      (uint32_t)((ch != ch0) || (k != 0)));
+                    }
+                }
+                umma2_commit_mc(&empty_b[stage], 3);     // frees the stage in both CTAs
+                if (++stage == kDa2Stages) { stage = 0; phase ^= 1; }
+            }
+            umma2_commit_mc(tmem_full, 3);
+        }
+    } else {                                             // ---------------- epilogue warps 2..5
+        const int q = warp & 3;
+        const int k = mt * 128 + q * 32 + lane;
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+        for (int c = 0; c < C; c += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(lane_addr + (uint32_t)c, r);
+            tmem_ld_wait();
+            if (k < N_a) {
+                float* o = d_ahat + (size_t)k * C + c;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                    red_add_v4(o + i, __uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                               __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();                          // nobody leaves while the pair may still touch its smem / TMEM
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc2(tmem_base, 512);
+    }
+}
+
 // ------------------------------------------------------------------ launch sequence
 int launch_grad_cells_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
                            int col_offset, int N_v, int N_a, int n_a_pad, int C, int P, HeadParams hp,
@@ -362,21 +477,36 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
     // stage 3: d_ahat (zeroed by the caller)
     {
         ProfScope _ps(kProfBwdDa, st);
+        const int n_mt = n_a_pad / kDaBM;
+        const bool pair = (n_mt % 2 == 0) && (C == 256 || C == 512) && !getenv("AVT_NO_PAIR");
+        const int bk = pair ? kDa2BK : kDaBK;
         CUtensorMap map_g, map_vt;
-        if (!make_tmap_bf16_2d(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, 64, kDaBK) ||
-            !make_tmap_bf16_2d(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, 64, kDaBK)) {
+        bool ok;
+        if (pair)
+            ok = make_tmap_bf16_blocks(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, bk, 2) &&
+                 make_tmap_bf16_blocks(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, bk, 2);
+        else
+            ok = make_tmap_bf16_2d(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, 64, bk) &&
+                 make_tmap_bf16_2d(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, 64, bk);
+        if (!ok) {
             set_error("bf16 backward: cuTensorMapEncodeTiled failed (d_ahat)");
             return AVT_ERR_CUDA;
         }
-        const int n_mt = n_a_pad / kDaBM;
-        const int n_chunks = (n_rows + kDaBK - 1) / kDaBK;
+        const int n_chunks = (n_rows + bk - 1) / bk;
         int splits = sms / n_mt;
         if (splits < 1) splits = 1;
         if (splits > n_chunks) splits = n_chunks;
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)kDaSmemBytes));
-        bwd_da_kernel<<<n_mt * splits, kDaThreads, kDaSmemBytes, st>>>(map_g, map_vt, d_ahat, N_a, n_mt,
-                                                                      splits, n_chunks, C);
+        if (pair) {
+            AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)kDa2SmemBytes));
+            bwd_da_pair_kernel<<<n_mt * splits, kDa2Threads, kDa2SmemBytes, st>>>(map_g, map_vt, d_ahat, N_a,
+                                                                                  n_mt, splits, n_chunks, C);
+        } else {
+            AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)kDaSmemBytes));
+            bwd_da_kernel<<<n_mt * splits, kDaThreads, kDaSmemBytes, st>>>(map_g, map_vt, d_ahat, N_a, n_mt,
+                                                                          splits, n_chunks, C);
+        }
         AVT_LAUNCH_CHECK();
     }
     return AVT_OK;

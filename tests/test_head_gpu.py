@@ -170,6 +170,25 @@ def test_ragged_shapes(n_v, n_a, precision):
     assert rel(r["logits"], o["logits"]) < TOL[precision][0]
 
 
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_anticorrelated_features_take_the_exact_path(precision):
+    """Every similarity negative (v = -|.|, a = +|.|): all tri-map weights fall below 2^-30,
+    the regime where the shared-reciprocal epilogue must hand over to the exact one
+    (weights of a ratio need RELATIVE accuracy)."""
+    n = 16
+    v, a = head_features(n, n, 71, "relu")
+    v = -v
+    v[: n // 2] = np.abs(v[: n // 2]) * np.where(np.arange(196) % 2 == 0, 1.0, -1.0).astype(np.float32)
+    o, dv, da = ho.head_forward_backward_torch(v, a)
+    r = run_head(v, a, precision, grad=True)
+    tol, gtol = TOL[precision]
+    assert np.isfinite(r["logits"]).all()
+    assert rel(r["logits"], o["logits"]) < max(tol, 5e-5)
+    assert abs(r["loss_rows"].mean() - o["loss"]) < max(tol, 5e-5) * max(1.0, abs(o["loss"]))
+    assert relnorm(r["dv"], dv) < gtol
+    assert relnorm(r["da"], da) < gtol
+
+
 def test_fused_loss_matches_head_and_is_linear_in_scale():
     from audio_visual_tubes_b200 import HeadConfig, hardway_loss
     v, a = head_features(16, 16, 61, "mix")
