@@ -200,6 +200,208 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
     }
 }
 
+// ------------------------------------------------------------------ stage 2, CTA pairs
+// cta_group::2 version: a cluster of two CTAs owns 256 consecutive rows of np (M = 256).  As in
+// the 1-CTA kernel the two halves of C are two passes over K into two 256-column accumulators,
+// so the epilogue of one half overlaps the MMAs of the other (a single-pass N = 512 variant
+// that reads G once was measured slower: with all 512 TMEM columns busy the write-heavy
+// epilogue serialises with the MMAs on every SM at the same time).  Per stage a CTA pulls its
+// own 128 rows of G (16 KB) and HALF of the a_hat^T chunk (16 KB): 32 KB for an M = 256 step
+// against 48 KB for an M = 128 step before.
+constexpr int kDv2BHalfBytes = 128 * kDvBK * 2;       // this CTA's 128 channel rows of one N = 256 MMA
+constexpr int kDv2StageBytes = kDvABytes + kDv2BHalfBytes;         // 32 KB
+constexpr int kDv2Stages = 6;
+constexpr size_t kDv2SmemBytes = 1024 + (size_t)kDv2Stages * kDv2StageBytes + 256 + 2 * 2 * kDvBM * 4;
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kDvThreads, 1)
+bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_at,
+                   const __nv_bfloat16* __restrict__ vt, const float* __restrict__ rnorm_v,
+                   float* __restrict__ dv, int n_rows, int n_tile_pairs, int KC, int C, int P) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* stages = base;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stages + (size_t)kDv2Stages * kDv2StageBytes);
+    uint64_t* full_b = bars;                             // leader's copy counts both CTAs' bytes
+    uint64_t* empty_b = bars + kDv2Stages;
+    uint64_t* tmem_full = bars + 2 * kDv2Stages;         // [2] one per half of C
+    uint64_t* tmem_empty = tmem_full + 2;                // [2] leader's copies: 256 local + 256 peer arrivals
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    float* t_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][2][128]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair0 = blockIdx.x >> 1, pair_step = gridDim.x >> 1;
+    const int nh = C / 256;                              // C is 256 or 512
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&map_g);
+        prefetch_tmap(&map_at);
+        for (int i = 0; i < kDv2Stages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 512); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc2(tmem_holder, 512);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+
+    if (warp == 0) {
+        if (lane == 0) {                                 // ---------------- TMA producer (both CTAs)
+            int stage = 0; uint32_t phase = 0;
+            for (int tp = pair0; tp < n_tile_pairs; tp += pair_step) {
+                const int tile = tp * 2 + (int)rank;
+                for (int h = 0; h < nh; ++h) {
+                    for (int kc = 0; kc < KC; ++kc) {
+                        mbar_wait(&empty_b[stage], phase ^ 1);
+                        if (rank == 0) mbar_arrive_expect_tx(&full_b[stage], (uint32_t)(2 * kDv2StageBytes));
+                        uint8_t* sA = stages + (size_t)stage * kDv2StageBytes;
+                        tma_load_2d_pair(sA, &map_g, &full_b[stage], kc * kDvBK, tile * kDvBM);
+                        tma_load_2d_pair(sA + kDvABytes, &map_at, &full_b[stage], kc * kDvBK,
+                                         h * 256 + (int)rank * 128);
+                        if (++stage == kDv2Stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {                    // ---------------- MMA issuer (leader only)
+            const uint32_t idesc = make_idesc_bf16(256, 256, 0, 0);
+            int stage = 0; uint32_t phase = 0, it = 0;
+            for (int tp = pair0; tp < n_tile_pairs; tp += pair_step, ++it) {
+                for (int h = 0; h < nh; ++h) {
+                    mbar_wait(&tmem_empty[h], (it & 1u) ^ 1u);
+                    tc_fence_after();
+                    for (int kc = 0; kc < KC; ++kc) {
+                        mbar_wait(&full_b[stage], phase);
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_u32(stages + (size_t)stage * kDv2StageBytes);
+                        const uint32_t b_addr = a_addr + kDvABytes;
+#pragma unroll
+                        for (int k = 0; k < kDvBK / 16; ++k) {
+                            const uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
+                            const uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
+                            umma2_bf16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                        }
+                        umma2_commit_mc(&empty_b[stage], 3);
+                        if (++stage == kDv2Stages) { stage = 0; phase ^= 1; }
+                    }
+                    umma2_commit_mc(&tmem_full[h], 3);
+                }
+            }
+        }
+    } else {                                             // ---------------- epilogue warps 2..9
+        const int q = warp & 3;
+        const int grp = (warp - 2) >> 2;
+        const int r_in = q * 32 + lane;
+        const uint32_t Pu = (uint32_t)P;
+        uint32_t it = 0;
+        for (int tp = pair0; tp < n_tile_pairs; tp += pair_step, ++it) {
+            const int row = (tp * 2 + (int)rank) * kDvBM + r_in;
+            const bool valid = row < n_rows;
+            const int rowc = row < n_rows ? row : n_rows - 1;
+            const int n = rowc / P;
+            const int p = rowc - n * P;
+            const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+            const __nv_bfloat16* vrow = vt + (size_t)rowc * C;
+            // v_hat row pieces are fetched ahead of their use: the first half before the
+            // accumulator is even ready, the second while the first is being reduced, and the
+            // second pass starts with the half that is still in registers.
+            uint32_t xa[4][16], xb[4][16];
+            const int ca = grp * 128, cb = 256 + grp * 128;        // this thread's columns of h = 0 / 1
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { ld_nc_v8(vrow + ca + 32 * j, xa[j]); ld_nc_v8(vrow + ca + 32 * j + 16, xa[j] + 8); }
+            if (nh == 2) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { ld_nc_v8(vrow + cb + 32 * j, xb[j]); ld_nc_v8(vrow + cb + 32 * j + 16, xb[j] + 8); }
+            }
+            mbar_wait(&tmem_full[0], it & 1u);
+            tc_fence_after();
+            float t = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                uint32_t r[32];
+                tmem_ld_32x32(lane_addr + (uint32_t)(ca + 32 * j), r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    t = fmaf(bf_lo(xa[j][e]), __uint_as_float(r[2 * e]), t);
+                    t = fmaf(bf_hi(xa[j][e]), __uint_as_float(r[2 * e + 1]), t);
+                }
+            }
+            if (nh == 2) {
+                mbar_wait(&tmem_full[1], it & 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(lane_addr + (uint32_t)(cb + 32 * j), r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        t = fmaf(bf_lo(xb[j][e]), __uint_as_float(r[2 * e]), t);
+                        t = fmaf(bf_hi(xb[j][e]), __uint_as_float(r[2 * e + 1]), t);
+                    }
+                }
+            }
+            float* tpart = t_part + (it & 1u) * 2 * kDvBM;
+            tpart[grp * kDvBM + r_in] = t;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            t = tpart[r_in] + tpart[kDvBM + r_in];
+            const float rn = rnorm_v[rowc];
+            const float rt = rn * t;
+            // pass 2: dv = rn * dv_hat - (rn t) * v_hat, NCHW fp32; each half is released as soon
+            // as it has been written so the next tile's MMAs can start on it
+            {
+                float* obase = dv + ((size_t)n * C + ca) * P + p;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(lane_addr + (uint32_t)(ca + 32 * j), r);
+                    tmem_ld_wait();
+                    float* o = obase + (uint32_t)(32 * j) * Pu;
+                    if (valid) {
+#pragma unroll
+                        for (int e = 0; e < 16; ++e) {
+                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-bf_lo(xa[j][e]), rt, rn * __uint_as_float(r[2 * e])));
+                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-bf_hi(xa[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
+                        }
+                    }
+                }
+                tc_fence_before();
+                if (rank == 0) mbar_arrive(&tmem_empty[0]); else mbar_arrive_leader(&tmem_empty[0]);
+            }
+            if (nh == 2) {
+                float* obase = dv + ((size_t)n * C + cb) * P + p;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(lane_addr + (uint32_t)(cb + 32 * j), r);
+                    tmem_ld_wait();
+                    float* o = obase + (uint32_t)(32 * j) * Pu;
+                    if (valid) {
+#pragma unroll
+                        for (int e = 0; e < 16; ++e) {
+                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-bf_lo(xb[j][e]), rt, rn * __uint_as_float(r[2 * e])));
+                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-bf_hi(xb[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
+                        }
+                    }
+                }
+                tc_fence_before();
+                if (rank == 0) mbar_arrive(&tmem_empty[1]); else mbar_arrive_leader(&tmem_empty[1]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc2(tmem_base, 512);
+    }
+}
+
 // ------------------------------------------------------------------ stage 3: d_ahat
 constexpr int kDaThreads = 192;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2..5 epilogue
 constexpr int kDaBM = 128;
@@ -460,18 +662,28 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
     // stage 2: dv
     {
         ProfScope _ps(kProfBwdDv, st);
+        const bool pair = (C == 256 || C == 512) && !getenv("AVT_NO_PAIR");
         CUtensorMap map_g, map_at;
         if (!make_tmap_bf16_2d(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, kDvBM) ||
-            !make_tmap_bf16_2d(&map_at, at_bf, (uint64_t)C, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, 256)) {
+            !make_tmap_bf16_2d(&map_at, at_bf, (uint64_t)C, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, pair ? 128 : 256)) {
             set_error("bf16 backward: cuTensorMapEncodeTiled failed (dv)");
             return AVT_ERR_CUDA;
         }
         const int n_tiles = (n_rows + kDvBM - 1) / kDvBM;
-        const int grid = n_tiles < sms ? n_tiles : sms;
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)kDvSmemBytes));
-        bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv, n_rows,
-                                                             n_tiles, n_a_pad / kDvBK, C, P);
+        if (pair) {
+            const int n_pairs = (n_tiles + 1) / 2;
+            const int grid_pairs = n_pairs < sms / 2 ? n_pairs : sms / 2;
+            AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)kDv2SmemBytes));
+            bwd_dv_pair_kernel<<<2 * grid_pairs, kDvThreads, kDv2SmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv,
+                                                                                  n_rows, n_pairs, n_a_pad / kDvBK, C, P);
+        } else {
+            const int grid = n_tiles < sms ? n_tiles : sms;
+            AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)kDvSmemBytes));
+            bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv, n_rows,
+                                                                 n_tiles, n_a_pad / kDvBK, C, P);
+        }
         AVT_LAUNCH_CHECK();
     }
     // stage 3: d_ahat (zeroed by the caller)
