@@ -203,6 +203,25 @@ def test_fused_loss_matches_head_and_is_linear_in_scale():
     assert relnorm(at.grad.cpu().numpy(), da) < 2e-4
 
 
+def test_graph_captured_step_equals_eager():
+    """HeadStep replays one captured CUDA graph; its outputs must equal the eager calls bit for
+    bit (same kernels, same order) and track new inputs written into the captured buffers."""
+    from audio_visual_tubes_b200 import HeadConfig, HeadStep, hardway_value_and_grad
+    v, a = head_features(24, 24, 81, "mix")
+    vt, at = torch.tensor(v, device="cuda"), torch.tensor(a, device="cuda")
+    cfg = HeadConfig()
+    hs = HeadStep(vt, at, cfg)
+    for seed in (81, 82):
+        v2, a2 = head_features(24, 24, seed, "mix")
+        vt.copy_(torch.tensor(v2)); at.copy_(torch.tensor(a2))
+        l0, dv0, da0 = hardway_value_and_grad(vt, at, cfg)
+        l1, dv1, da1 = hs()
+        torch.cuda.synchronize()
+        assert torch.equal(l0, l1) and torch.equal(dv0, dv1)
+        # d_ahat is reduced with floating-point atomics: equal up to summation order
+        assert relnorm(da1.cpu().numpy(), da0.cpu().numpy()) < 1e-5
+
+
 def test_errors_are_loud():
     from audio_visual_tubes_b200 import HeadConfig, hardway_head
     v, a = head_features(2, 2, 1, "relu")
