@@ -26,20 +26,21 @@ constexpr int kNpix = kDst * kDst;               // 50176
 constexpr int kRank = kNpix / 2;                 // int(224*224/2), train_hardway_1frame.py:202
 constexpr int kEvThreads = 224;                  // 56 column quads x 4 row groups
 constexpr int kEvWarps = kEvThreads / 32;        // 7
-constexpr int kRowsPerGroup = kDst / 4;          // 56
-constexpr int kCap = 15 * kEvThreads;            // 3360 candidates (4-bit private counters)
+constexpr int kQuads = kDst / 4;                 // 56 column quads per row
+constexpr int kStrips = 28;                      // 8-row strips per column quad (2 edges + 13 x 2 halves)
+constexpr int kCap = 3072;                       // candidate keys kept for the exact refinement
 constexpr int kSampleSide = 56;                  // every 4th pixel in x and y
 constexpr int kNs = kSampleSide * kSampleSide;   // 3136 samples (14 per thread)
-constexpr int kMargin = 80;                      // sample ranks either side of the median
-constexpr int kBins = 64;
+constexpr int kSampPerThread = kNs / kEvThreads; // 14
+constexpr int kMargin = 32;                      // sample ranks either side of the median
+constexpr int kHist = 256;
 constexpr int kMaxBoxesSmem = 32;
 
 struct EvalSmem {
     float m[kSrc * kSrc];                        // the 14x14 map
     float rows[kSrc][kDst];                      // horizontally interpolated rows
-    uint32_t list[kCap];                         // sample keys, later candidate keys
-    uint32_t cnt[kBins / 8][kEvThreads];         // private nibble counters, bank = thread
-    uint32_t whist[kEvWarps][kBins];
+    uint32_t list[kCap];                         // candidate keys inside the bracket
+    uint32_t hist[2][kHist];                     // shared-atomic histograms (two, to save a barrier)
     uint32_t red[4][kEvWarps];
     uint32_t bcast[4];
     int n_list;
@@ -72,90 +73,86 @@ __device__ __forceinline__ float lerp_rn(float a, float w0, float b, float w1) {
     return __fadd_rn(__fmul_rn(a, w0), __fmul_rn(b, w1));
 }
 
-__device__ __forceinline__ uint32_t block_sum_u(uint32_t x, uint32_t* red) {
+// Three block reductions behind ONE pair of barriers: sum of x, min of lo, max of hi.
+__device__ __forceinline__ void block_sum_min_max(EvalSmem& S, uint32_t& x, uint32_t& lo, uint32_t& hi) {
     x = __reduce_add_sync(0xffffffffu, x);
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
     __syncthreads();
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = x;
+    if ((threadIdx.x & 31) == 0) {
+        const int w = threadIdx.x >> 5;
+        S.red[0][w] = x; S.red[1][w] = lo; S.red[2][w] = hi;
+    }
     __syncthreads();
-    uint32_t t = 0;
+    x = 0; lo = 0xffffffffu; hi = 0u;
 #pragma unroll
-    for (int i = 0; i < kEvWarps; ++i) t += red[i];
-    return t;
+    for (int i = 0; i < kEvWarps; ++i) {
+        x += S.red[0][i]; lo = min(lo, S.red[1][i]); hi = max(hi, S.red[2][i]);
+    }
 }
-__device__ __forceinline__ uint32_t block_min_u(uint32_t x, uint32_t* red) {
-    x = __reduce_min_sync(0xffffffffu, x);
+__device__ __forceinline__ void block_sum3(EvalSmem& S, uint32_t& a, uint32_t& b, uint32_t& c) {
+    a = __reduce_add_sync(0xffffffffu, a);
+    b = __reduce_add_sync(0xffffffffu, b);
+    c = __reduce_add_sync(0xffffffffu, c);
     __syncthreads();
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = x;
+    if ((threadIdx.x & 31) == 0) {
+        const int w = threadIdx.x >> 5;
+        S.red[0][w] = a; S.red[1][w] = b; S.red[2][w] = c;
+    }
     __syncthreads();
-    uint32_t t = red[0];
+    a = b = c = 0;
 #pragma unroll
-    for (int i = 1; i < kEvWarps; ++i) t = min(t, red[i]);
-    return t;
-}
-__device__ __forceinline__ uint32_t block_max_u(uint32_t x, uint32_t* red) {
-    x = __reduce_max_sync(0xffffffffu, x);
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = x;
-    __syncthreads();
-    uint32_t t = red[0];
-#pragma unroll
-    for (int i = 1; i < kEvWarps; ++i) t = max(t, red[i]);
-    return t;
+    for (int i = 0; i < kEvWarps; ++i) { a += S.red[0][i]; b += S.red[1][i]; c += S.red[2][i]; }
 }
 
-// r-th smallest (0-based, among the keys inside [lo, hi]) of list[0..n).  Exact: each
-// round histograms the top <= 6 undecided bits into 64 bins with conflict-free private
-// 4-bit counters (a thread sees <= 15 keys), then descends into the bin holding rank r.
+// Every warp scans the same 256-bin histogram (8 bins per lane) and returns the bin that
+// holds rank r (0-based) plus the number of entries in the bins before it.  r >= total
+// returns bin 255.  No barrier: the caller has already synchronised on the histogram.
+__device__ __forceinline__ void scan256(const uint32_t* hist, uint32_t r, int& bin, uint32_t& before) {
+    const int lane = threadIdx.x & 31;
+    const uint4 c0 = reinterpret_cast<const uint4*>(hist)[2 * lane];
+    const uint4 c1 = reinterpret_cast<const uint4*>(hist)[2 * lane + 1];
+    const uint32_t c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    uint32_t tot = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) tot += c[q];
+    uint32_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const uint32_t ball = __ballot_sync(0xffffffffu, incl > r);
+    const int owner = ball ? __ffs(ball) - 1 : 31;
+    uint32_t e = incl - tot;
+    int b = 0;
+#pragma unroll
+    for (int q = 0; q < 7; ++q)
+        if (b == q && r >= e + c[q]) { e += c[q]; ++b; }
+    bin = 8 * owner + __shfl_sync(0xffffffffu, b, owner);
+    before = __shfl_sync(0xffffffffu, e, owner);
+}
+
+// r-th smallest (0-based) of the keys in list[0..n) that lie inside [lo, hi].  Exact radix
+// descent, 8 bits per round, histogram by shared-memory atomics (n is a few hundred to a few
+// thousand keys spread over the bins, so conflicts are rare).
 __device__ uint32_t list_select(EvalSmem& S, int n, uint32_t r, uint32_t lo, uint32_t hi) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int round = 0; round < 8 && lo != hi; ++round) {      // <= 6 rounds cover 32 bits
+    const int tid = threadIdx.x;
+    while (lo != hi) {
         const uint32_t span = hi - lo;
-        const int s = max(0, (32 - __clz(span)) - 6);        // (span >> s) < 64
-#pragma unroll
-        for (int w = 0; w < kBins / 8; ++w) S.cnt[w][tid] = 0u;
+        const int s = max(0, (32 - __clz(span)) - 8);            // (span >> s) < 256
+        __syncthreads();                                         // previous round's readers are done
+        for (int i = tid; i < kHist; i += kEvThreads) S.hist[0][i] = 0u;
+        __syncthreads();
         for (int i = tid; i < n; i += kEvThreads) {
-            uint32_t key = S.list[i];
-            if (key >= lo && key <= hi) {
-                uint32_t b = (key - lo) >> s;
-                S.cnt[b >> 3][tid] += 1u << ((b & 7u) * 4u);
-            }
-        }
-        uint32_t mine0 = 0, mine1 = 0;
-#pragma unroll
-        for (int w = 0; w < kBins / 8; ++w) {
-            uint32_t word = S.cnt[w][tid];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                uint32_t tot = __reduce_add_sync(0xffffffffu, (word >> (4 * q)) & 15u);
-                const int b = w * 8 + q;
-                if ((b & 31) == lane) { if (b < 32) mine0 = tot; else mine1 = tot; }
-            }
-        }
-        S.whist[warp][lane] = mine0;
-        S.whist[warp][lane + 32] = mine1;
-        __syncthreads();
-        if (warp == 0) {
-            uint32_t c0 = 0, c1 = 0;
-#pragma unroll
-            for (int w = 0; w < kEvWarps; ++w) { c0 += S.whist[w][lane]; c1 += S.whist[w][lane + 32]; }
-            uint32_t i0 = c0, i1 = c1;                       // inclusive scans over lanes
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                uint32_t a = __shfl_up_sync(0xffffffffu, i0, o);
-                uint32_t b = __shfl_up_sync(0xffffffffu, i1, o);
-                if (lane >= o) { i0 += a; i1 += b; }
-            }
-            const uint32_t tot0 = __shfl_sync(0xffffffffu, i0, 31);
-            const uint32_t e0 = i0 - c0, e1 = tot0 + i1 - c1;    // exclusive prefix of each bin
-            const bool h0 = (r >= e0 && r < e0 + c0), h1 = (r >= e1 && r < e1 + c1);
-            if (h0) { S.bcast[0] = lane; S.bcast[1] = e0; }
-            if (h1) { S.bcast[0] = lane + 32; S.bcast[1] = e1; }
-            if (!__any_sync(0xffffffffu, h0 || h1) && lane == 0) { S.bcast[0] = 0; S.bcast[1] = 0; }
+            const uint32_t key = S.list[i];
+            if (key >= lo && key <= hi) atomicAdd(&S.hist[0][(key - lo) >> s], 1u);
         }
         __syncthreads();
-        const uint32_t b = S.bcast[0];
-        r -= S.bcast[1];
-        const uint32_t nlo = lo + (b << s);
+        int b; uint32_t before;
+        scan256(S.hist[0], r, b, before);
+        r -= before;
+        const uint32_t nlo = lo + ((uint32_t)b << s);
         uint32_t nhi = nlo + ((1u << s) - 1u);
         if (nhi < nlo) nhi = 0xffffffffu;
         lo = nlo;
@@ -164,49 +161,88 @@ __device__ uint32_t list_select(EvalSmem& S, int n, uint32_t r, uint32_t lo, uin
     return lo;
 }
 
-// One sweep over all 50176 pixels: c_lt = #(key < blo), c_in = #(blo <= key <= bhi),
-// key range, and (optionally) the in-bracket keys appended to S.list (first kCap only).
-__device__ void full_pass(EvalSmem& S, uint32_t blo, uint32_t bhi, bool collect,
-                          uint32_t& c_lt, uint32_t& c_in, uint32_t& kmin, uint32_t& kmax) {
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int cg = tid % 56, rg = tid / 56;
+// Visit every destination row of this thread's 7 strips (4 pixels wide, 8 rows tall).
+// Vertical weights repeat with period 16, so a strip between source rows s and s+1 loads its
+// two float4 operands ONCE and uses compile-time weights (2r+1)/32; the second half of an
+// interval is the first half mirrored (operands swapped, rows visited downwards) -- the same
+// products and the same sum as tap()/lerp_rn, bit for bit.  Rows 0..7 and 216..223 clamp.
+template <int kUnroll, class RowFn>
+__device__ __forceinline__ void for_each_row(const EvalSmem& S, RowFn&& fn) {
+    const int cq = threadIdx.x % kQuads, rg = threadIdx.x / kQuads;
+#pragma unroll 1
+    for (int j = 0; j < kStrips / 4; ++j) {
+        const int strip = 4 * j + rg;
+        const bool edge = (strip == 0 || strip == kStrips - 1);
+        const int s = (strip - 1) >> 1, half = (strip - 1) & 1;
+        // operand rows: edges clamp (value = a*1 + b*0 for all 8 rows); second halves swap
+        const int ra = edge ? (strip ? kSrc - 1 : 0) : s + half;
+        const int rb = edge ? (strip ? kSrc - 1 : 1) : s + 1 - half;
+        const float4 a = *reinterpret_cast<const float4*>(&S.rows[ra][4 * cq]);
+        const float4 b = *reinterpret_cast<const float4*>(&S.rows[rb][4 * cq]);
+        int y = edge ? (strip ? kDst - 8 : 0) : 16 * s + 8 + (half ? 15 : 0);
+        const int ystep = (!edge && half) ? -1 : 1;
+        const float dw = edge ? 0.0f : (1.0f / 16.0f);
+        float w1 = edge ? 0.0f : (1.0f / 32.0f), w0 = 1.0f - w1;    // multiples of 1/32: exact
+#pragma unroll kUnroll
+        for (int r = 0; r < 8; ++r) {
+            float4 u;
+            u.x = lerp_rn(a.x, w0, b.x, w1); u.y = lerp_rn(a.y, w0, b.y, w1);
+            u.z = lerp_rn(a.z, w0, b.z, w1); u.w = lerp_rn(a.w, w0, b.w, w1);
+            fn(y, u);
+            y += ystep; w1 += dw; w0 -= dw;
+        }
+    }
+}
+
+// Generic counting sweep in KEY space (fallback path only): c_in = #(blo <= key <= bhi),
+// c_lt = #(key < blo), key range, and optionally the in-bracket keys appended to S.list.
+__device__ void full_pass_keys(EvalSmem& S, uint32_t blo, uint32_t bhi, bool collect,
+                               uint32_t& c_lt, uint32_t& c_in, uint32_t& kmin, uint32_t& kmax) {
     uint32_t n_lt = 0, n_in = 0, mn = 0xffffffffu, mx = 0u;
-    if (tid == 0) S.n_list = 0;
     __syncthreads();
-    for (int yy = 0; yy < kRowsPerGroup; ++yy) {
-        const int y = rg * kRowsPerGroup + yy;
-        int s0, s1; float w0, w1;
-        tap(y, s0, s1, w0, w1);
-        const float4 a = *reinterpret_cast<const float4*>(&S.rows[s0][4 * cg]);
-        const float4 b = *reinterpret_cast<const float4*>(&S.rows[s1][4 * cg]);
-        const float u[4] = {lerp_rn(a.x, w0, b.x, w1), lerp_rn(a.y, w0, b.y, w1),
-                            lerp_rn(a.z, w0, b.z, w1), lerp_rn(a.w, w0, b.w, w1)};
+    if (threadIdx.x == 0) S.n_list = 0;
+    __syncthreads();
+    for_each_row<1>(S, [&](int, const float4& u) {
+        const float uu[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const uint32_t key = f2key(u[j]);
+            const uint32_t key = f2key(uu[j]);
             mn = min(mn, key); mx = max(mx, key);
             n_lt += (key < blo);
             const bool in = (key >= blo) && (key <= bhi);
             n_in += in;
-            if (collect) {
-                const uint32_t hit = __ballot_sync(0xffffffffu, in);
-                if (hit) {
-                    int base = 0;
-                    const int leader = __ffs(hit) - 1;
-                    if (lane == leader) base = atomicAdd(&S.n_list, __popc(hit));
-                    base = __shfl_sync(0xffffffffu, base, leader);
-                    if (in) {
-                        const int idx = base + __popc(hit & ((1u << lane) - 1u));
-                        if (idx < kCap) S.list[idx] = key;
-                    }
-                }
+            if (collect && in) {
+                const int idx = atomicAdd(&S.n_list, 1);
+                if (idx < kCap) S.list[idx] = key;
             }
         }
+    });
+    block_sum_min_max(S, n_lt, mn, mx);
+    c_lt = n_lt; kmin = mn; kmax = mx;
+    uint32_t z0 = 0, z1 = 0;
+    block_sum3(S, n_in, z0, z1);
+    c_in = n_in;
+}
+
+// Exact k-th key by counted bisection over the key range until the rest fits the list.
+// Slow (several sweeps) but unconditional: NaN / Inf maps, constant maps, huge tie groups
+// and the rare miss of the sampled bracket come here.
+__device__ uint32_t select_generic(EvalSmem& S, uint32_t& kmin, uint32_t& kmax) {
+    uint32_t a, b;
+    full_pass_keys(S, 0u, 0xffffffffu, false, a, b, kmin, kmax);
+    uint32_t lo = kmin, hi = kmax, c_lo = 0, n_in = kNpix;
+    for (;;) {
+        if (lo == hi) return lo;
+        uint32_t c, d;
+        if (n_in <= (uint32_t)kCap) {
+            full_pass_keys(S, lo, hi, true, a, b, c, d);
+            return list_select(S, (int)n_in, (uint32_t)kRank - c_lo, lo, hi);
+        }
+        const uint32_t mid = lo + (hi - lo) / 2u;
+        full_pass_keys(S, lo, mid, false, a, b, c, d);            // b = #(lo <= key <= mid)
+        if ((uint32_t)kRank - c_lo < b) { hi = mid; n_in = b; }
+        else { lo = mid + 1u; c_lo += b; n_in -= b; }
     }
-    c_lt = block_sum_u(n_lt, S.red[0]);
-    c_in = block_sum_u(n_in, S.red[1]);
-    kmin = block_min_u(mn, S.red[2]);
-    kmax = block_max_u(mx, S.red[3]);
 }
 
 // f of the header comment: utils.py:234-239 applied to -u, then pred = 1 - h
@@ -216,8 +252,50 @@ __device__ __forceinline__ float pred_of(float u, bool normalised, float vmin_h,
     return __fsub_rn(1.0f, h);
 }
 
+// Final sweep: materialise, binarise, read / rasterise the GT, count.  kKeyCmp selects the
+// comparison: float compare against t_on (finite maps), or key compare against k_on.
+template <bool kDenseGt, bool kKeyCmp>
+__device__ __forceinline__ void final_sweep(const EvalSmem& S, uint32_t k_on, float t_on, int nb, int gt_mode,
+                                            float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
+                                            const uint8_t* __restrict__ gt_i,
+                                            uint32_t& inter, uint32_t& gsum, uint32_t& zc) {
+    const int cq = threadIdx.x % kQuads;
+    for_each_row<4>(S, [&](int y, const float4& u) {
+        const size_t o = (size_t)y * kDst + 4 * cq;
+        if (up_o) __stcs(reinterpret_cast<float4*>(up_o + o), u);
+        uint32_t m4;
+        if (kKeyCmp)
+            m4 = (f2key(u.x) >= k_on ? 1u : 0u) | (f2key(u.y) >= k_on ? 0x100u : 0u) |
+                 (f2key(u.z) >= k_on ? 0x10000u : 0u) | (f2key(u.w) >= k_on ? 0x1000000u : 0u);
+        else
+            m4 = (u.x >= t_on ? 1u : 0u) | (u.y >= t_on ? 0x100u : 0u) |
+                 (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
+        if (mk_o) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
+        uint32_t g4;
+        if (kDenseGt) {
+            g4 = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + o));
+        } else {
+            g4 = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int x = 4 * cq + j;
+                int c = 0;
+                for (int q = 0; q < nb; ++q)
+                    c += (x >= S.boxes[q][0] && x < S.boxes[q][2] && y >= S.boxes[q][1] && y < S.boxes[q][3]);
+                if (gt_mode == AVT_GT_VGGSS) c = min(c, 1);
+                else if (gt_mode == AVT_GT_FLICKR) c = min(c, 2);
+                else c = min(c, 255);
+                g4 |= (uint32_t)c << (8 * j);
+            }
+        }
+        inter = __dp4a(m4, g4, inter);
+        gsum = __dp4a(g4, 0x01010101u, gsum);
+        zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
+    });
+}
+
 template <bool kDenseGt>
-__global__ void __launch_bounds__(kEvThreads)
+__global__ void __maxnreg__(48)
 eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restrict__ gt_dense,
                  const int16_t* __restrict__ boxes, const uint8_t* __restrict__ box_count,
                  int max_boxes, int gt_mode, float* __restrict__ up224, uint8_t* __restrict__ mask,
@@ -225,143 +303,172 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
                  double* __restrict__ ciou) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EvalSmem& S = *reinterpret_cast<EvalSmem*>(smem_raw);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int cg = tid % 56, rg = tid / 56;
+    const int tid = threadIdx.x;
 
     for (int map = blockIdx.x; map < N; map += gridDim.x) {
-        __syncthreads();
-        if (tid < kSrc * kSrc) S.m[tid] = maps14[(size_t)map * kSrc * kSrc + tid];
+        // ---- load the map; source range and finiteness (one barrier pair)
+        uint32_t bad = 0, kmn = 0xffffffffu, kmx = 0u;
+        if (tid < kSrc * kSrc) {
+            const float x = maps14[(size_t)map * kSrc * kSrc + tid];
+            S.m[tid] = x;
+            bad = !(fabsf(x) <= 3.402823466e38f);
+            kmn = kmx = f2key(x);
+        }
         int nb = 0;
         if (!kDenseGt) {
             nb = min((int)box_count[map], min(max_boxes, kMaxBoxesSmem));
             if (tid < nb * 4)
                 (&S.boxes[0][0])[tid] = boxes[((size_t)map * max_boxes) * 4 + tid];
         }
-        __syncthreads();
-        // horizontal pass: rows[j][x] = m[j][sx0]*(1-wx) + m[j][sx1]*wx
+        for (int i = tid; i < 2 * kHist; i += kEvThreads) (&S.hist[0][0])[i] = 0u;
+        if (tid == 0) S.n_list = 0;
+        block_sum_min_max(S, bad, kmn, kmx);                     // also publishes S.m
+        // ---- horizontal pass: rows[j][x] = m[j][sx0]*(1-wx) + m[j][sx1]*wx
         {
             int s0, s1; float w0, w1;
-            tap(tid, s0, s1, w0, w1);                        // tid == destination column
+            tap(tid, s0, s1, w0, w1);                            // tid == destination column
 #pragma unroll
             for (int j = 0; j < kSrc; ++j)
                 S.rows[j][tid] = lerp_rn(S.m[j * kSrc + s0], w0, S.m[j * kSrc + s1], w1);
         }
         __syncthreads();
-        // ---- bracket the median from a 56x56 sub-sample
-        uint32_t smn = 0xffffffffu, smx = 0u;
-        for (int i = tid; i < kNs; i += kEvThreads) {
-            const int sy = 4 * (i / kSampleSide) + 2, sx = 4 * (i % kSampleSide) + 1;
-            int s0, s1; float w0, w1;
-            tap(sy, s0, s1, w0, w1);
-            const uint32_t key = f2key(lerp_rn(S.rows[s0][sx], w0, S.rows[s1][sx], w1));
-            S.list[i] = key;
-            smn = min(smn, key); smx = max(smx, key);
-        }
-        smn = block_min_u(smn, S.red[0]);
-        smx = block_max_u(smx, S.red[1]);
-        const uint32_t blo = list_select(S, kNs, kNs / 2 - kMargin, smn, smx);
-        const uint32_t bhi = list_select(S, kNs, kNs / 2 + kMargin, smn, smx);
-        // ---- count and collect
-        uint32_t c_lt, c_in, kmin, kmax;
-        full_pass(S, blo, bhi, true, c_lt, c_in, kmin, kmax);
-        uint32_t kstar;
-        if (c_lt <= (uint32_t)kRank && (uint32_t)kRank < c_lt + c_in && c_in <= (uint32_t)kCap) {
-            kstar = list_select(S, (int)c_in, (uint32_t)kRank - c_lt, blo, bhi);
-        } else {
-            // exact fallback: counted bisection over the key range until the rest fits the list
-            uint32_t lo, hi, c_lo, n_in;
-            if ((uint32_t)kRank < c_lt) { lo = kmin; hi = blo - 1u; c_lo = 0; n_in = c_lt; }
-            else if ((uint32_t)kRank >= c_lt + c_in) { lo = bhi + 1u; hi = kmax; c_lo = c_lt + c_in; n_in = kNpix - c_lo; }
-            else { lo = blo; hi = bhi; c_lo = c_lt; n_in = c_in; }
-            for (;;) {
-                if (lo == hi) { kstar = lo; break; }
-                uint32_t a, b, c, d;
-                if (n_in <= (uint32_t)kCap) {
-                    full_pass(S, lo, hi, true, a, b, c, d);
-                    kstar = list_select(S, (int)n_in, (uint32_t)kRank - c_lo, lo, hi);
-                    break;
+
+        uint32_t kstar = 0, kmin = 0, kmax = 0;
+        const float smin = key2f(kmn), smax = key2f(kmx);
+        const float span = smax - smin;
+        bool done = false;
+        if (bad == 0u && span > 0.0f && span <= 3.402823466e38f) {
+            // ---- bracket the median from a 56x56 sub-sample held in registers.  Two rounds of a
+            // 256-bin linear histogram; the bracket only has to CONTAIN the true rank (checked
+            // below with exact counts), so its construction is free to be approximate.
+            float sm[kSampPerThread];
+#pragma unroll
+            for (int k = 0; k < kSampPerThread; ++k) {
+                const int p = ((tid + kEvThreads * k) * 1117) % kNs;      // scatter lanes over the image
+                const int sy = 4 * (p / kSampleSide) + 2, sx = 4 * (p % kSampleSide) + 1;
+                int s0, s1; float w0, w1;
+                tap(sy, s0, s1, w0, w1);
+                sm[k] = lerp_rn(S.rows[s0][sx], w0, S.rows[s1][sx], w1);
+            }
+            const float scale1 = 256.0f / span, inv1 = span * (1.0f / 256.0f);
+#pragma unroll
+            for (int k = 0; k < kSampPerThread; ++k) {
+                const int b = min(kHist - 1, max(0, __float2int_rd((sm[k] - smin) * scale1)));
+                atomicAdd(&S.hist[0][b], 1u);
+            }
+            __syncthreads();
+            int bl, bh; uint32_t before;
+            scan256(S.hist[0], (uint32_t)(kNs / 2 - kMargin), bl, before);
+            scan256(S.hist[0], (uint32_t)(kNs / 2 + kMargin), bh, before);
+            const float lo2 = smin + (float)bl * inv1, hi2 = smin + (float)(bh + 1) * inv1;
+            const float span2 = hi2 - lo2;
+            const float scale2 = 254.0f / span2, inv2 = span2 * (1.0f / 254.0f);
+            // bins 1..254 tile [lo2, hi2); bin 0 = below, bin 255 = above
+#pragma unroll
+            for (int k = 0; k < kSampPerThread; ++k) {
+                const int b = min(kHist - 1, max(0, __float2int_rd((sm[k] - lo2) * scale2) + 1));
+                atomicAdd(&S.hist[1][b], 1u);
+            }
+            __syncthreads();
+            int sl, sh;
+            scan256(S.hist[1], (uint32_t)(kNs / 2 - kMargin), sl, before);
+            scan256(S.hist[1], (uint32_t)(kNs / 2 + kMargin), sh, before);
+            const float ninf = __uint_as_float(0xff800000u), pinf = __uint_as_float(0x7f800000u);
+            const float tlo = (sl == 0 || !(span2 > 0.0f)) ? ninf : lo2 + (float)(sl - 1) * inv2;
+            const float thi = (sh == kHist - 1 || !(span2 > 0.0f)) ? pinf : lo2 + (float)sh * inv2;
+            // ---- counting sweep: c_lt = #(u < tlo), range, candidates tlo <= u < thi -> S.list
+            uint32_t n_lt = 0;
+            float fmn = pinf, fmx = ninf;
+            for_each_row<2>(S, [&](int, const float4& u) {
+                const float gmx = fmaxf(fmaxf(u.x, u.y), fmaxf(u.z, u.w));
+                const float gmn = fminf(fminf(u.x, u.y), fminf(u.z, u.w));
+                fmx = fmaxf(fmx, gmx); fmn = fminf(fmn, gmn);
+                if (gmx < tlo) {
+                    n_lt += 4;                                   // whole quad below the bracket
+                } else if (gmn < thi) {                          // quad touches the bracket
+                    const float uu[4] = {u.x, u.y, u.z, u.w};
+                    float cand[4];
+                    int c = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const bool below = uu[j] < tlo;
+                        n_lt += below;
+                        if (!below && uu[j] < thi) {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) if (q == c) cand[q] = uu[j];
+                            ++c;
+                        }
+                    }
+                    if (c) {
+                        const int base = atomicAdd(&S.n_list, c);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            if (q < c && base + q < kCap) S.list[base + q] = f2key(cand[q]);
+                    }
                 }
-                const uint32_t mid = lo + (hi - lo) / 2u;
-                full_pass(S, lo, mid, false, a, b, c, d);        // b = #(lo <= key <= mid)
-                if ((uint32_t)kRank - c_lo < b) { hi = mid; n_in = b; }
-                else { lo = mid + 1u; c_lo += b; n_in -= b; }
+            });
+            kmin = f2key(fmn); kmax = f2key(fmx);
+            block_sum_min_max(S, n_lt, kmin, kmax);
+            const uint32_t c_lt = n_lt, c_in = (uint32_t)S.n_list;
+            if (c_lt <= (uint32_t)kRank && (uint32_t)kRank < c_lt + c_in && c_in <= (uint32_t)kCap) {
+                // any superset of the candidates' key range will do (+-0 compare equal as floats)
+                const uint32_t klo = (tlo == 0.0f) ? f2key(-0.0f) : f2key(tlo);
+                const uint32_t khi = (thi == 0.0f) ? f2key(0.0f) : f2key(thi);
+                kstar = list_select(S, (int)c_in, (uint32_t)kRank - c_lt, klo, khi);
+                done = true;
             }
         }
-        // ---- threshold in pred space, and the first key whose pixel is switched on
+        if (!done) kstar = select_generic(S, kmin, kmax);
+
+        // ---- threshold in pred space, and the first key whose pixel is switched on.  pred is
+        // monotone non-decreasing in the key, so gallop + bisect from kstar (every thread does
+        // the same few evaluations; typically on(kstar + 1) settles it).
         const float umin = key2f(kmin), umax = key2f(kmax);
         const float vmin_h = -umax;
         const float range = __fsub_rn(-umin, vmin_h);           // vmax - vmin, utils.py:237
         const bool normalised = !(range == 0.0f);
         const float thr = pred_of(key2f(kstar), normalised, vmin_h, range);
-        if (warp == 0) {
-            // smallest key K in [kmin, kmax+1] with (pred > thr or pred >= 1); 32-way search
-            uint32_t lo = kmin, hi = kmax + 1u;
-            while (lo < hi) {
-                const uint32_t step = (hi - lo) / 32u + 1u;
-                const uint64_t pk = (uint64_t)lo + (uint64_t)lane * step;
-                bool on = true;
-                if (pk < (uint64_t)hi) {
-                    const float pr = pred_of(key2f((uint32_t)pk), normalised, vmin_h, range);
-                    on = (pr > thr) || (pr >= 1.0f);
-                }
-                const uint32_t ball = __ballot_sync(0xffffffffu, on);
-                const int j = ball ? __ffs(ball) - 1 : 32;       // 32: every probe was valid and off
-                if (j == 0) { hi = lo; }
-                else {
-                    const uint64_t nh = (uint64_t)lo + (uint64_t)j * step;
-                    const uint32_t nl = lo + (uint32_t)(j - 1) * step + 1u;
-                    if (nh < (uint64_t)hi) hi = (uint32_t)nh;
-                    lo = nl;
-                }
+        auto on = [&](uint64_t k) -> bool {
+            if (k > (uint64_t)kmax) return true;
+            const float pr = pred_of(key2f((uint32_t)k), normalised, vmin_h, range);
+            return (pr > thr) || (pr >= 1.0f);
+        };
+        uint64_t lo, hi;                                         // keys < lo are off, hi is on
+        if (on(kstar)) {
+            hi = kstar; lo = kmin;
+            uint64_t step = 1;
+            while (hi > (uint64_t)kmin) {
+                const uint64_t c = (hi - kmin > step) ? hi - step : (uint64_t)kmin;
+                if (on(c)) { hi = c; step <<= 1; } else { lo = c + 1; break; }
             }
-            if (lane == 0) S.bcast[2] = lo;
+            if (hi == (uint64_t)kmin) lo = hi;
+        } else {
+            lo = (uint64_t)kstar + 1; hi = (uint64_t)kmax + 1;
+            uint64_t step = 1;
+            while (lo < hi) {
+                const uint64_t c = lo + step - 1;
+                if (c >= hi) break;
+                if (on(c)) { hi = c; break; } else { lo = c + 1; step <<= 1; }
+            }
         }
-        __syncthreads();
-        const uint32_t k_on = S.bcast[2];
+        while (lo < hi) {
+            const uint64_t mid = lo + (hi - lo) / 2;
+            if (on(mid)) hi = mid; else lo = mid + 1;
+        }
+        const bool all_off = lo > 0xffffffffull;                 // only when kmax is the last key
+        const uint32_t k_on = all_off ? 0xffffffffu : (uint32_t)lo;
+        const float t_on = key2f(k_on);
+        const bool key_cmp = (bad != 0u) || all_off || k_on == f2key(0.0f);
+
         // ---- final sweep: materialise, binarise, count
         const int gt_den = (gt_mode == AVT_GT_FLICKR) ? 2 : 1;
         uint32_t inter = 0, gsum = 0, zc = 0;
         float* up_o = up224 ? up224 + (size_t)map * kNpix : nullptr;
         uint8_t* mk_o = mask ? mask + (size_t)map * kNpix : nullptr;
         const uint8_t* gt_i = kDenseGt ? gt_dense + (size_t)map * kNpix : nullptr;
-        for (int yy = 0; yy < kRowsPerGroup; ++yy) {
-            const int y = rg * kRowsPerGroup + yy;
-            int s0, s1; float w0, w1;
-            tap(y, s0, s1, w0, w1);
-            const float4 a = *reinterpret_cast<const float4*>(&S.rows[s0][4 * cg]);
-            const float4 b = *reinterpret_cast<const float4*>(&S.rows[s1][4 * cg]);
-            float4 u;
-            u.x = lerp_rn(a.x, w0, b.x, w1); u.y = lerp_rn(a.y, w0, b.y, w1);
-            u.z = lerp_rn(a.z, w0, b.z, w1); u.w = lerp_rn(a.w, w0, b.w, w1);
-            const size_t o = (size_t)y * kDst + 4 * cg;
-            if (up_o) __stcs(reinterpret_cast<float4*>(up_o + o), u);
-            uint32_t m4 = (f2key(u.x) >= k_on ? 1u : 0u) | (f2key(u.y) >= k_on ? 0x100u : 0u) |
-                          (f2key(u.z) >= k_on ? 0x10000u : 0u) | (f2key(u.w) >= k_on ? 0x1000000u : 0u);
-            if (mk_o) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
-            uint32_t g4;
-            if (kDenseGt) {
-                g4 = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + o));
-            } else {
-                g4 = 0;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int x = 4 * cg + j;
-                    int c = 0;
-                    for (int q = 0; q < nb; ++q)
-                        c += (x >= S.boxes[q][0] && x < S.boxes[q][2] && y >= S.boxes[q][1] && y < S.boxes[q][3]);
-                    if (gt_mode == AVT_GT_VGGSS) c = min(c, 1);
-                    else if (gt_mode == AVT_GT_FLICKR) c = min(c, 2);
-                    else c = min(c, 255);
-                    g4 |= (uint32_t)c << (8 * j);
-                }
-            }
-            inter = __dp4a(m4, g4, inter);
-            gsum = __dp4a(g4, 0x01010101u, gsum);
-            zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
-        }
-        inter = block_sum_u(inter, S.red[0]);
-        gsum = block_sum_u(gsum, S.red[1]);
-        zc = block_sum_u(zc, S.red[2]);
+        if (key_cmp) final_sweep<kDenseGt, true>(S, k_on, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc);
+        else final_sweep<kDenseGt, false>(S, k_on, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc);
+        block_sum3(S, inter, gsum, zc);
         if (tid == 0) {
             const uint32_t uni = gsum + (uint32_t)gt_den * zc;
             inter_w[map] = (int32_t)inter;
@@ -524,7 +631,7 @@ extern "C" int avt_eval_maps(const float* maps14, int N, const uint8_t* gt_dense
     int dev = 0, sms = 148;
     AVT_CHECK_CUDA(cudaGetDevice(&dev));
     AVT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int grid = N < sms * 6 ? N : sms * 6;           // 6 resident blocks per SM
+    const int grid = N < sms * 7 ? N : sms * 7;           // 7 resident blocks per SM
     ProfScope _ps(kProfEval, st);
     if (gt_dense) {
         AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<true>,
