@@ -28,13 +28,16 @@ constexpr int kEvThreads = 224;                  // 56 column quads x 4 row grou
 constexpr int kEvWarps = kEvThreads / 32;        // 7
 constexpr int kQuads = kDst / 4;                 // 56 column quads per row
 constexpr int kStrips = 28;                      // 8-row strips per column quad (2 edges + 13 x 2 halves)
-constexpr int kCap = 3072;                       // candidate keys kept for the exact refinement
+constexpr int kCap = 2048;                       // candidate keys kept for the exact refinement
 constexpr int kSampleSide = 56;                  // every 4th pixel in x and y
 constexpr int kNs = kSampleSide * kSampleSide;   // 3136 samples (14 per thread)
 constexpr int kSampPerThread = kNs / kEvThreads; // 14
-constexpr int kMargin = 32;                      // sample ranks either side of the median
+constexpr int kMargin = 24;                      // sample ranks either side of the median
 constexpr int kHist = 256;
 constexpr int kMaxBoxesSmem = 32;
+
+// [0] maps that took the generic (bisection) selection, [1] maps evaluated -- dev statistics
+__device__ unsigned long long g_eval_stats[2];
 
 struct EvalSmem {
     float m[kSrc * kSrc];                        // the 14x14 map
@@ -166,8 +169,8 @@ __device__ uint32_t list_select(EvalSmem& S, int n, uint32_t r, uint32_t lo, uin
 // two float4 operands ONCE and uses compile-time weights (2r+1)/32; the second half of an
 // interval is the first half mirrored (operands swapped, rows visited downwards) -- the same
 // products and the same sum as tap()/lerp_rn, bit for bit.  Rows 0..7 and 216..223 clamp.
-template <int kUnroll, class RowFn>
-__device__ __forceinline__ void for_each_row(const EvalSmem& S, RowFn&& fn) {
+template <int kUnroll, class StripFn, class RowFn>
+__device__ __forceinline__ void for_each_row(const EvalSmem& S, StripFn&& pre, RowFn&& fn) {
     const int cq = threadIdx.x % kQuads, rg = threadIdx.x / kQuads;
 #pragma unroll 1
     for (int j = 0; j < kStrips / 4; ++j) {
@@ -183,12 +186,13 @@ __device__ __forceinline__ void for_each_row(const EvalSmem& S, RowFn&& fn) {
         const int ystep = (!edge && half) ? -1 : 1;
         const float dw = edge ? 0.0f : (1.0f / 16.0f);
         float w1 = edge ? 0.0f : (1.0f / 32.0f), w0 = 1.0f - w1;    // multiples of 1/32: exact
+        pre(y, ystep);
 #pragma unroll kUnroll
         for (int r = 0; r < 8; ++r) {
             float4 u;
             u.x = lerp_rn(a.x, w0, b.x, w1); u.y = lerp_rn(a.y, w0, b.y, w1);
             u.z = lerp_rn(a.z, w0, b.z, w1); u.w = lerp_rn(a.w, w0, b.w, w1);
-            fn(y, u);
+            fn(r, y, u);
             y += ystep; w1 += dw; w0 -= dw;
         }
     }
@@ -202,7 +206,7 @@ __device__ void full_pass_keys(EvalSmem& S, uint32_t blo, uint32_t bhi, bool col
     __syncthreads();
     if (threadIdx.x == 0) S.n_list = 0;
     __syncthreads();
-    for_each_row<1>(S, [&](int, const float4& u) {
+    for_each_row<1>(S, [](int, int) {}, [&](int, int, const float4& u) {
         const float uu[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -252,42 +256,107 @@ __device__ __forceinline__ float pred_of(float u, bool normalised, float vmin_h,
     return __fsub_rn(1.0f, h);
 }
 
-// Final sweep: materialise, binarise, read / rasterise the GT, count.  kKeyCmp selects the
-// comparison: float compare against t_on (finite maps), or key compare against k_on.
-template <bool kDenseGt, bool kKeyCmp>
-__device__ __forceinline__ void final_sweep(const EvalSmem& S, uint32_t k_on, float t_on, int nb, int gt_mode,
+// One thread's strip: 4 pixels wide, 8 rows tall, between two source rows (see for_each_row).
+struct Strip {
+    float4 a, b;
+    int y0, ystep;
+    float w1_0, dw;
+};
+__device__ __forceinline__ Strip strip_load(const EvalSmem& S, int j) {
+    const int cq = threadIdx.x % kQuads, rg = threadIdx.x / kQuads;
+    const int strip = 4 * j + rg;
+    const bool edge = (strip == 0 || strip == kStrips - 1);
+    const int s = (strip - 1) >> 1, half = (strip - 1) & 1;
+    const int ra = edge ? (strip ? kSrc - 1 : 0) : s + half;
+    const int rb = edge ? (strip ? kSrc - 1 : 1) : s + 1 - half;
+    Strip t;
+    t.a = *reinterpret_cast<const float4*>(&S.rows[ra][4 * cq]);
+    t.b = *reinterpret_cast<const float4*>(&S.rows[rb][4 * cq]);
+    t.y0 = edge ? (strip ? kDst - 8 : 0) : 16 * s + 8 + (half ? 15 : 0);
+    t.ystep = (!edge && half) ? -1 : 1;
+    t.dw = edge ? 0.0f : (1.0f / 16.0f);
+    t.w1_0 = edge ? 0.0f : (1.0f / 32.0f);
+    return t;
+}
+__device__ __forceinline__ float4 strip_row(const Strip& t, int r) {
+    const float w1 = fmaf((float)r, t.dw, t.w1_0), w0 = 1.0f - w1;   // multiples of 1/32: exact
+    float4 u;
+    u.x = lerp_rn(t.a.x, w0, t.b.x, w1); u.y = lerp_rn(t.a.y, w0, t.b.y, w1);
+    u.z = lerp_rn(t.a.z, w0, t.b.z, w1); u.w = lerp_rn(t.a.w, w0, t.b.w, w1);
+    return u;
+}
+
+__device__ __forceinline__ uint32_t boxes_quad(const EvalSmem& S, int nb, int gt_mode, int x0, int y) {
+    uint32_t g4 = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int x = x0 + j;
+        int c = 0;
+        for (int q = 0; q < nb; ++q)
+            c += (x >= S.boxes[q][0] && x < S.boxes[q][2] && y >= S.boxes[q][1] && y < S.boxes[q][3]);
+        if (gt_mode == AVT_GT_VGGSS) c = min(c, 1);
+        else if (gt_mode == AVT_GT_FLICKR) c = min(c, 2);
+        else c = min(c, 255);
+        g4 |= (uint32_t)c << (8 * j);
+    }
+    return g4;
+}
+
+// Final sweep: materialise, binarise, read / rasterise the GT, count.  Straight-line per strip:
+// the 8 GT words of a strip are requested before any arithmetic, the up-sampled row is computed
+// once and feeds the store, the compare and the counts.
+template <bool kDenseGt, bool kUp, bool kMask>
+__device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int nb, int gt_mode,
                                             float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
                                             const uint8_t* __restrict__ gt_i,
                                             uint32_t& inter, uint32_t& gsum, uint32_t& zc) {
     const int cq = threadIdx.x % kQuads;
-    for_each_row<4>(S, [&](int y, const float4& u) {
-        const size_t o = (size_t)y * kDst + 4 * cq;
-        if (up_o) __stcs(reinterpret_cast<float4*>(up_o + o), u);
-        uint32_t m4;
-        if (kKeyCmp)
-            m4 = (f2key(u.x) >= k_on ? 1u : 0u) | (f2key(u.y) >= k_on ? 0x100u : 0u) |
-                 (f2key(u.z) >= k_on ? 0x10000u : 0u) | (f2key(u.w) >= k_on ? 0x1000000u : 0u);
-        else
-            m4 = (u.x >= t_on ? 1u : 0u) | (u.y >= t_on ? 0x100u : 0u) |
-                 (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
-        if (mk_o) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
-        uint32_t g4;
-        if (kDenseGt) {
-            g4 = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + o));
-        } else {
-            g4 = 0;
+#pragma unroll 1
+    for (int j = 0; j < kStrips / 4; ++j) {
+        const Strip t = strip_load(S, j);
+        const int o0 = t.y0 * kDst + 4 * cq, os = t.ystep * kDst;
+#pragma unroll 1
+        for (int h = 0; h < 8; h += 4) {
+            uint32_t g[4];
+            if (kDenseGt) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int x = 4 * cq + j;
-                int c = 0;
-                for (int q = 0; q < nb; ++q)
-                    c += (x >= S.boxes[q][0] && x < S.boxes[q][2] && y >= S.boxes[q][1] && y < S.boxes[q][3]);
-                if (gt_mode == AVT_GT_VGGSS) c = min(c, 1);
-                else if (gt_mode == AVT_GT_FLICKR) c = min(c, 2);
-                else c = min(c, 255);
-                g4 |= (uint32_t)c << (8 * j);
+                for (int r = 0; r < 4; ++r)
+                    g[r] = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (o0 + (h + r) * os)));
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const float4 u = strip_row(t, h + r);
+                const int o = o0 + (h + r) * os;
+                if (kUp) __stcs(reinterpret_cast<float4*>(up_o + o), u);
+                uint32_t m4;
+                m4 = (u.x >= t_on ? 1u : 0u) | (u.y >= t_on ? 0x100u : 0u) |
+                         (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
+                if (kMask) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
+                const uint32_t g4 = kDenseGt ? g[r] : boxes_quad(S, nb, gt_mode, 4 * cq, t.y0 + (h + r) * t.ystep);
+                inter = __dp4a(m4, g4, inter);
+                gsum = __dp4a(g4, 0x01010101u, gsum);
+                zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
             }
         }
+    }
+}
+
+// Key-compare variant of the final sweep for the rare maps that need it (NaN / Inf values, a
+// threshold exactly at +0): same outputs, pointers tested at run time, no unrolling.
+template <bool kDenseGt>
+__device__ __noinline__ void final_sweep_keys(const EvalSmem& S, uint32_t k_on, int nb, int gt_mode,
+                                              float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
+                                              const uint8_t* __restrict__ gt_i,
+                                              uint32_t& inter, uint32_t& gsum, uint32_t& zc) {
+    const int cq = threadIdx.x % kQuads;
+    for_each_row<1>(S, [](int, int) {}, [&](int, int y, const float4& u) {
+        const int o = y * kDst + 4 * cq;
+        if (up_o) __stcs(reinterpret_cast<float4*>(up_o + o), u);
+        const uint32_t m4 = (f2key(u.x) >= k_on ? 1u : 0u) | (f2key(u.y) >= k_on ? 0x100u : 0u) |
+                            (f2key(u.z) >= k_on ? 0x10000u : 0u) | (f2key(u.w) >= k_on ? 0x1000000u : 0u);
+        if (mk_o) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
+        const uint32_t g4 = kDenseGt ? __ldcs(reinterpret_cast<const unsigned int*>(gt_i + o))
+                                     : boxes_quad(S, nb, gt_mode, 4 * cq, y);
         inter = __dp4a(m4, g4, inter);
         gsum = __dp4a(g4, 0x01010101u, gsum);
         zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
@@ -376,41 +445,45 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             const float ninf = __uint_as_float(0xff800000u), pinf = __uint_as_float(0x7f800000u);
             const float tlo = (sl == 0 || !(span2 > 0.0f)) ? ninf : lo2 + (float)(sl - 1) * inv2;
             const float thi = (sh == kHist - 1 || !(span2 > 0.0f)) ? pinf : lo2 + (float)sh * inv2;
-            // ---- counting sweep: c_lt = #(u < tlo), range, candidates tlo <= u < thi -> S.list
+            // ---- counting sweep: quads entirely below the bracket are counted four at a time and
+            // quads entirely above cost nothing; the few lanes whose quad touches [tlo, thi) count
+            // exactly and append their in-bracket pixels (raw float bits) to S.list.
             uint32_t n_lt = 0;
             float fmn = pinf, fmx = ninf;
-            for_each_row<2>(S, [&](int, const float4& u) {
-                const float gmx = fmaxf(fmaxf(u.x, u.y), fmaxf(u.z, u.w));
-                const float gmn = fminf(fminf(u.x, u.y), fminf(u.z, u.w));
-                fmx = fmaxf(fmx, gmx); fmn = fminf(fmn, gmn);
-                if (gmx < tlo) {
-                    n_lt += 4;                                   // whole quad below the bracket
-                } else if (gmn < thi) {                          // quad touches the bracket
-                    const float uu[4] = {u.x, u.y, u.z, u.w};
-                    float cand[4];
-                    int c = 0;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const bool below = uu[j] < tlo;
-                        n_lt += below;
-                        if (!below && uu[j] < thi) {
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) if (q == c) cand[q] = uu[j];
-                            ++c;
+#pragma unroll 1
+            for (int j = 0; j < kStrips / 4; ++j) {
+                const Strip t = strip_load(S, j);
+#pragma unroll 4
+                for (int r = 0; r < 8; ++r) {
+                    const float4 u = strip_row(t, r);
+                    const float gmx = fmaxf(fmaxf(u.x, u.y), fmaxf(u.z, u.w));
+                    const float gmn = fminf(fminf(u.x, u.y), fminf(u.z, u.w));
+                    fmx = fmaxf(fmx, gmx); fmn = fminf(fmn, gmn);
+                    if (gmx < tlo) {
+                        n_lt += 4;
+                    } else if (gmn < thi) {
+                        const bool b0 = u.x < tlo, b1 = u.y < tlo, b2 = u.z < tlo, b3 = u.w < tlo;
+                        const bool i0 = !b0 && u.x < thi, i1 = !b1 && u.y < thi;
+                        const bool i2 = !b2 && u.z < thi, i3 = !b3 && u.w < thi;
+                        n_lt += (int)b0 + (int)b1 + (int)b2 + (int)b3;
+                        const int c = (int)i0 + (int)i1 + (int)i2 + (int)i3;
+                        if (c) {
+                            int p = atomicAdd(&S.n_list, c);
+                            if (p + c <= kCap) {
+                                if (i0) S.list[p++] = __float_as_uint(u.x);
+                                if (i1) S.list[p++] = __float_as_uint(u.y);
+                                if (i2) S.list[p++] = __float_as_uint(u.z);
+                                if (i3) S.list[p] = __float_as_uint(u.w);
+                            }
                         }
                     }
-                    if (c) {
-                        const int base = atomicAdd(&S.n_list, c);
-#pragma unroll
-                        for (int q = 0; q < 4; ++q)
-                            if (q < c && base + q < kCap) S.list[base + q] = f2key(cand[q]);
-                    }
                 }
-            });
+            }
             kmin = f2key(fmn); kmax = f2key(fmx);
-            block_sum_min_max(S, n_lt, kmin, kmax);
+            block_sum_min_max(S, n_lt, kmin, kmax);              // its barriers also publish the list
             const uint32_t c_lt = n_lt, c_in = (uint32_t)S.n_list;
             if (c_lt <= (uint32_t)kRank && (uint32_t)kRank < c_lt + c_in && c_in <= (uint32_t)kCap) {
+                for (int i = tid; i < (int)c_in; i += kEvThreads) S.list[i] = f2key(__uint_as_float(S.list[i]));
                 // any superset of the candidates' key range will do (+-0 compare equal as floats)
                 const uint32_t klo = (tlo == 0.0f) ? f2key(-0.0f) : f2key(tlo);
                 const uint32_t khi = (thi == 0.0f) ? f2key(0.0f) : f2key(thi);
@@ -419,6 +492,7 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             }
         }
         if (!done) kstar = select_generic(S, kmin, kmax);
+        if (tid == 0) { if (!done) atomicAdd(&g_eval_stats[0], 1ull); atomicAdd(&g_eval_stats[1], 1ull); }
 
         // ---- threshold in pred space, and the first key whose pixel is switched on.  pred is
         // monotone non-decreasing in the key, so gallop + bisect from kstar (every thread does
@@ -466,8 +540,14 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
         float* up_o = up224 ? up224 + (size_t)map * kNpix : nullptr;
         uint8_t* mk_o = mask ? mask + (size_t)map * kNpix : nullptr;
         const uint8_t* gt_i = kDenseGt ? gt_dense + (size_t)map * kNpix : nullptr;
-        if (key_cmp) final_sweep<kDenseGt, true>(S, k_on, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc);
-        else final_sweep<kDenseGt, false>(S, k_on, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc);
+#define AVT_FINAL(UP, MK) final_sweep<kDenseGt, UP, MK>(S, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc)
+        if (key_cmp) {
+            final_sweep_keys<kDenseGt>(S, k_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc);
+        } else {
+            if (up_o) { if (mk_o) AVT_FINAL(true, true); else AVT_FINAL(true, false); }
+            else { if (mk_o) AVT_FINAL(false, true); else AVT_FINAL(false, false); }
+        }
+#undef AVT_FINAL
         block_sum3(S, inter, gsum, zc);
         if (tid == 0) {
             const uint32_t uni = gsum + (uint32_t)gt_den * zc;
@@ -636,17 +716,34 @@ extern "C" int avt_eval_maps(const float* maps14, int N, const uint8_t* gt_dense
     if (gt_dense) {
         AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<true>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<true>,
+                                            cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            (int)cudaSharedmemCarveoutMaxShared));
         eval_maps_kernel<true><<<grid, kEvThreads, smem, st>>>(maps14, N, gt_dense, boxes, box_count,
                                                               max_boxes, gt_mode, up224, mask, inter_w,
                                                               union_w, ciou);
     } else {
         AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<false>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<false>,
+                                            cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            (int)cudaSharedmemCarveoutMaxShared));
         eval_maps_kernel<false><<<grid, kEvThreads, smem, st>>>(maps14, N, gt_dense, boxes, box_count,
                                                                max_boxes, gt_mode, up224, mask, inter_w,
                                                                union_w, ciou);
     }
     AVT_LAUNCH_CHECK();
+    return AVT_OK;
+}
+
+extern "C" int avt_eval_stats(unsigned long long* out2, int reset) {
+    AVT_REQUIRE(out2, "avt_eval_stats: null pointer");
+    AVT_CHECK_CUDA(cudaDeviceSynchronize());
+    AVT_CHECK_CUDA(cudaMemcpyFromSymbol(out2, g_eval_stats, sizeof(unsigned long long) * 2));
+    if (reset) {
+        const unsigned long long z[2] = {0ull, 0ull};
+        AVT_CHECK_CUDA(cudaMemcpyToSymbol(g_eval_stats, z, sizeof(z)));
+    }
     return AVT_OK;
 }
 

@@ -146,6 +146,12 @@ int avt_eval_maps(const float* maps14, int N,
                   float* up224, uint8_t* mask,
                   int32_t* inter_w, int32_t* union_w, double* ciou, void* stream);
 
+/* Selection statistics of avt_eval_maps since the last reset (host array of 2):
+ *   out2[0] = maps whose median-rank threshold (train_hardway_1frame.py:202, np.sort(...)[25088])
+ *             needed the generic counted-bisection path instead of the sampled bracket,
+ *   out2[1] = maps evaluated.  Synchronises the device; diagnostics only. */
+int avt_eval_stats(unsigned long long* out2, int reset);
+
 /* Evaluator.cal_CIOU(infer, gtmap, thres) (utils.py:209-214) on N ready-made 224x224 fp32
  * maps: infer_map = (infer >= thres); gt = gt_w / gt_den with gt_w uint8 weights.
  * inter_w / union_w / ciou as in avt_eval_maps. */

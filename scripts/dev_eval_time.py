@@ -28,7 +28,12 @@ def run(mode):
              _lib.ptr(up) if mode == "mat" else None, _lib.ptr(mk) if mode == "mat" else None)
     _lib.check(lib.avt_eval_maps(*a, _lib.ptr(iw), _lib.ptr(uw), _lib.ptr(ci), _lib.stream_ptr()), "avt_eval_maps")
 
+import ctypes
+st = (ctypes.c_ulonglong * 2)()
+lib.avt_eval_stats(st, 1)
 run("mat"); torch.cuda.synchronize()
+lib.avt_eval_stats(st, 1)
+print(f"generic-path maps: {st[0]} of {st[1]}")
 g_np = gt[0].cpu().numpy()
 bad = 0
 for i in range(0, n, max(1, n // 40)):
