@@ -28,7 +28,7 @@ constexpr int kEvThreads = 224;                  // 56 column quads x 4 row grou
 constexpr int kEvWarps = kEvThreads / 32;        // 7
 constexpr int kQuads = kDst / 4;                 // 56 column quads per row
 constexpr int kStrips = 28;                      // 8-row strips per column quad (2 edges + 13 x 2 halves)
-constexpr int kCap = 2048;                       // candidate keys kept for the exact refinement
+constexpr int kCap = 6144;                       // candidate keys kept for the exact refinement
 constexpr int kSampleSide = 56;                  // every 4th pixel in x and y
 constexpr int kNs = kSampleSide * kSampleSide;   // 3136 samples (14 per thread)
 constexpr int kSampPerThread = kNs / kEvThreads; // 14
@@ -46,6 +46,7 @@ struct EvalSmem {
     uint32_t hist[2][kHist];                     // shared-atomic histograms (two, to save a barrier)
     uint32_t red[4][kEvWarps];
     uint32_t bcast[4];
+    uint32_t geo[kStrips];                       // packed strip geometry (strip_pack)
     int n_list;
     int16_t boxes[kMaxBoxesSmem][4];
 };
@@ -262,18 +263,31 @@ struct Strip {
     int y0, ystep;
     float w1_0, dw;
 };
-__device__ __forceinline__ Strip strip_load(const EvalSmem& S, int j) {
-    const int cq = threadIdx.x % kQuads, rg = threadIdx.x / kQuads;
-    const int strip = 4 * j + rg;
+// Strip geometry is the same for every map: 28 packed words in shared memory, written once per
+// block.  bits 0-7 y0, bit 8 rows run downwards, bits 12-15 / 16-19 operand rows, bit 20 edge.
+__device__ __forceinline__ uint32_t strip_pack(int strip) {
     const bool edge = (strip == 0 || strip == kStrips - 1);
     const int s = (strip - 1) >> 1, half = (strip - 1) & 1;
     const int ra = edge ? (strip ? kSrc - 1 : 0) : s + half;
     const int rb = edge ? (strip ? kSrc - 1 : 1) : s + 1 - half;
+    const int y0 = edge ? (strip ? kDst - 8 : 0) : 16 * s + 8 + (half ? 15 : 0);
+    return (uint32_t)y0 | ((!edge && half) ? 0x100u : 0u) | ((uint32_t)ra << 12) | ((uint32_t)rb << 16) |
+           (edge ? 0x100000u : 0u);
+}
+__device__ __forceinline__ void strip_geometry(const EvalSmem& S, int j, int& y0, int& ystep) {
+    const uint32_t g = S.geo[4 * j + threadIdx.x / kQuads];
+    y0 = (int)(g & 0xffu);
+    ystep = 1 - (int)((g >> 7) & 2u);
+}
+__device__ __forceinline__ Strip strip_load(const EvalSmem& S, int j) {
+    const int cq = threadIdx.x % kQuads;
+    const uint32_t g = S.geo[4 * j + threadIdx.x / kQuads];
     Strip t;
-    t.a = *reinterpret_cast<const float4*>(&S.rows[ra][4 * cq]);
-    t.b = *reinterpret_cast<const float4*>(&S.rows[rb][4 * cq]);
-    t.y0 = edge ? (strip ? kDst - 8 : 0) : 16 * s + 8 + (half ? 15 : 0);
-    t.ystep = (!edge && half) ? -1 : 1;
+    t.a = *reinterpret_cast<const float4*>(&S.rows[(g >> 12) & 15u][4 * cq]);
+    t.b = *reinterpret_cast<const float4*>(&S.rows[(g >> 16) & 15u][4 * cq]);
+    t.y0 = (int)(g & 0xffu);
+    t.ystep = 1 - (int)((g >> 7) & 2u);
+    const bool edge = (g & 0x100000u) != 0u;
     t.dw = edge ? 0.0f : (1.0f / 16.0f);
     t.w1_0 = edge ? 0.0f : (1.0f / 32.0f);
     return t;
@@ -311,44 +325,55 @@ __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int n
                                             const uint8_t* __restrict__ gt_i,
                                             uint32_t& inter, uint32_t& gsum, uint32_t& zc) {
     const int cq = threadIdx.x % kQuads;
+    uint4 g = make_uint4(0, 0, 0, 0), gn = g;
+    auto request = [&](int k) -> uint4 {                        // GT words of half-strip k
+        int y0, ystep;
+        strip_geometry(S, k >> 1, y0, ystep);
+        const int ob = (y0 + (k & 1) * 4 * ystep) * kDst + 4 * cq, os = ystep * kDst;
+        uint4 d;
+        d.x = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + ob));
+        d.y = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (ob + os)));
+        d.z = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (ob + 2 * os)));
+        d.w = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (ob + 3 * os)));
+        return d;
+    };
+    if (kDenseGt) g = request(0);
 #pragma unroll 1
-    for (int j = 0; j < kStrips / 4; ++j) {
-        const Strip t = strip_load(S, j);
-        const int o0 = t.y0 * kDst + 4 * cq, os = t.ystep * kDst;
-#pragma unroll 1
-        for (int h = 0; h < 8; h += 4) {
-            uint32_t g[4];
-            if (kDenseGt) {
+    for (int k = 0; k < 2 * (kStrips / 4); ++k) {
+        if (kDenseGt && k + 1 < 2 * (kStrips / 4)) gn = request(k + 1);   // one half-strip ahead
+        const Strip t = strip_load(S, k >> 1);
+        const int h = (k & 1) * 4;
+        const int ob = (t.y0 + h * t.ystep) * kDst + 4 * cq, os = t.ystep * kDst;
+        const float w1_h = fmaf((float)h, t.dw, t.w1_0);
 #pragma unroll
-                for (int r = 0; r < 4; ++r)
-                    g[r] = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (o0 + (h + r) * os)));
-            }
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const float4 u = strip_row(t, h + r);
-                const int o = o0 + (h + r) * os;
-                if (kUp) __stcs(reinterpret_cast<float4*>(up_o + o), u);
-                uint32_t m4;
-                m4 = (u.x >= t_on ? 1u : 0u) | (u.y >= t_on ? 0x100u : 0u) |
-                         (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
-                if (kMask) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
-                const uint32_t g4 = kDenseGt ? g[r] : boxes_quad(S, nb, gt_mode, 4 * cq, t.y0 + (h + r) * t.ystep);
-                inter = __dp4a(m4, g4, inter);
-                gsum = __dp4a(g4, 0x01010101u, gsum);
-                zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
-            }
+        for (int r = 0; r < 4; ++r) {
+            const float w1 = fmaf((float)r, t.dw, w1_h), w0 = 1.0f - w1;
+            float4 u;
+            u.x = lerp_rn(t.a.x, w0, t.b.x, w1); u.y = lerp_rn(t.a.y, w0, t.b.y, w1);
+            u.z = lerp_rn(t.a.z, w0, t.b.z, w1); u.w = lerp_rn(t.a.w, w0, t.b.w, w1);
+            const int o = ob + r * os;
+            if (kUp) __stcs(reinterpret_cast<float4*>(up_o + o), u);
+            const uint32_t m4 = (u.x >= t_on ? 1u : 0u) | (u.y >= t_on ? 0x100u : 0u) |
+                                (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
+            if (kMask) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
+            const uint32_t gr = (r == 0) ? g.x : (r == 1) ? g.y : (r == 2) ? g.z : g.w;
+            const uint32_t g4 = kDenseGt ? gr : boxes_quad(S, nb, gt_mode, 4 * cq, t.y0 + (h + r) * t.ystep);
+            inter = __dp4a(m4, g4, inter);
+            gsum = __dp4a(g4, 0x01010101u, gsum);
+            zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
         }
+        if (kDenseGt) g = gn;
     }
 }
 
 // Key-compare variant of the final sweep for the rare maps that need it (NaN / Inf values, a
 // threshold exactly at +0): same outputs, pointers tested at run time, no unrolling.
 template <bool kDenseGt>
-__device__ __noinline__ void final_sweep_keys(const EvalSmem& S, uint32_t k_on, int nb, int gt_mode,
-                                              float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
-                                              const uint8_t* __restrict__ gt_i,
-                                              uint32_t& inter, uint32_t& gsum, uint32_t& zc) {
+__device__ __noinline__ uint3 final_sweep_keys(const EvalSmem& S, uint32_t k_on, int nb, int gt_mode,
+                                               float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
+                                               const uint8_t* __restrict__ gt_i) {
     const int cq = threadIdx.x % kQuads;
+    uint32_t inter = 0, gsum = 0, zc = 0;
     for_each_row<1>(S, [](int, int) {}, [&](int, int y, const float4& u) {
         const int o = y * kDst + 4 * cq;
         if (up_o) __stcs(reinterpret_cast<float4*>(up_o + o), u);
@@ -361,6 +386,7 @@ __device__ __noinline__ void final_sweep_keys(const EvalSmem& S, uint32_t k_on, 
         gsum = __dp4a(g4, 0x01010101u, gsum);
         zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
     });
+    return make_uint3(inter, gsum, zc);
 }
 
 template <bool kDenseGt>
@@ -373,6 +399,7 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EvalSmem& S = *reinterpret_cast<EvalSmem*>(smem_raw);
     const int tid = threadIdx.x;
+    if (tid < kStrips) S.geo[tid] = strip_pack(tid);           // published by the first barrier below
 
     for (int map = blockIdx.x; map < N; map += gridDim.x) {
         // ---- load the map; source range and finiteness (one barrier pair)
@@ -446,8 +473,8 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             const float tlo = (sl == 0 || !(span2 > 0.0f)) ? ninf : lo2 + (float)(sl - 1) * inv2;
             const float thi = (sh == kHist - 1 || !(span2 > 0.0f)) ? pinf : lo2 + (float)sh * inv2;
             // ---- counting sweep: quads entirely below the bracket are counted four at a time and
-            // quads entirely above cost nothing; the few lanes whose quad touches [tlo, thi) count
-            // exactly and append their in-bracket pixels (raw float bits) to S.list.
+            // quads entirely above cost nothing; the few lanes whose quad touches [tlo, thi) append
+            // it WHOLE (one shared atomic + one 16-byte store: no per-pixel work under divergence).
             uint32_t n_lt = 0;
             float fmn = pinf, fmx = ninf;
 #pragma unroll 1
@@ -462,33 +489,31 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
                     if (gmx < tlo) {
                         n_lt += 4;
                     } else if (gmn < thi) {
-                        const bool b0 = u.x < tlo, b1 = u.y < tlo, b2 = u.z < tlo, b3 = u.w < tlo;
-                        const bool i0 = !b0 && u.x < thi, i1 = !b1 && u.y < thi;
-                        const bool i2 = !b2 && u.z < thi, i3 = !b3 && u.w < thi;
-                        n_lt += (int)b0 + (int)b1 + (int)b2 + (int)b3;
-                        const int c = (int)i0 + (int)i1 + (int)i2 + (int)i3;
-                        if (c) {
-                            int p = atomicAdd(&S.n_list, c);
-                            if (p + c <= kCap) {
-                                if (i0) S.list[p++] = __float_as_uint(u.x);
-                                if (i1) S.list[p++] = __float_as_uint(u.y);
-                                if (i2) S.list[p++] = __float_as_uint(u.z);
-                                if (i3) S.list[p] = __float_as_uint(u.w);
-                            }
-                        }
+                        const int p = atomicAdd(&S.n_list, 4);
+                        if (p + 4 <= kCap) *reinterpret_cast<float4*>(&S.list[p]) = u;
                     }
                 }
             }
             kmin = f2key(fmn); kmax = f2key(fmx);
             block_sum_min_max(S, n_lt, kmin, kmax);              // its barriers also publish the list
-            const uint32_t c_lt = n_lt, c_in = (uint32_t)S.n_list;
-            if (c_lt <= (uint32_t)kRank && (uint32_t)kRank < c_lt + c_in && c_in <= (uint32_t)kCap) {
-                for (int i = tid; i < (int)c_in; i += kEvThreads) S.list[i] = f2key(__uint_as_float(S.list[i]));
-                // any superset of the candidates' key range will do (+-0 compare equal as floats)
-                const uint32_t klo = (tlo == 0.0f) ? f2key(-0.0f) : f2key(tlo);
-                const uint32_t khi = (thi == 0.0f) ? f2key(0.0f) : f2key(thi);
-                kstar = list_select(S, (int)c_in, (uint32_t)kRank - c_lt, klo, khi);
-                done = true;
+            // full-lane post-pass over the collected quads: keys in place, exact counts.  Float
+            // order == key order except between -0 and +0, so a bracket edge at zero goes generic.
+            const int n = S.n_list;
+            if (n <= kCap && tlo != 0.0f && thi != 0.0f) {
+                const uint32_t klo = f2key(tlo), khi = f2key(thi) - 1u;
+                uint32_t below = 0, inside = 0, unused = 0;
+                for (int i = tid; i < n; i += kEvThreads) {
+                    const uint32_t key = f2key(__uint_as_float(S.list[i]));
+                    S.list[i] = key;
+                    below += (key < klo);
+                    inside += (key >= klo && key <= khi);
+                }
+                block_sum3(S, below, inside, unused);
+                const uint32_t c_lt = n_lt + below;
+                if (c_lt <= (uint32_t)kRank && (uint32_t)kRank < c_lt + inside) {
+                    kstar = list_select(S, n, (uint32_t)kRank - c_lt, klo, khi);
+                    done = true;
+                }
             }
         }
         if (!done) kstar = select_generic(S, kmin, kmax);
@@ -542,7 +567,8 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
         const uint8_t* gt_i = kDenseGt ? gt_dense + (size_t)map * kNpix : nullptr;
 #define AVT_FINAL(UP, MK) final_sweep<kDenseGt, UP, MK>(S, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc)
         if (key_cmp) {
-            final_sweep_keys<kDenseGt>(S, k_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc);
+            const uint3 c3 = final_sweep_keys<kDenseGt>(S, k_on, nb, gt_mode, up_o, mk_o, gt_i);
+            inter = c3.x; gsum = c3.y; zc = c3.z;
         } else {
             if (up_o) { if (mk_o) AVT_FINAL(true, true); else AVT_FINAL(true, false); }
             else { if (mk_o) AVT_FINAL(false, true); else AVT_FINAL(false, false); }
@@ -711,27 +737,21 @@ extern "C" int avt_eval_maps(const float* maps14, int N, const uint8_t* gt_dense
     int dev = 0, sms = 148;
     AVT_CHECK_CUDA(cudaGetDevice(&dev));
     AVT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int grid = N < sms * 7 ? N : sms * 7;           // 7 resident blocks per SM
     ProfScope _ps(kProfEval, st);
-    if (gt_dense) {
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<true>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<true>,
-                                            cudaFuncAttributePreferredSharedMemoryCarveout,
+    auto launch = [&](auto kernel) -> int {
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                             (int)cudaSharedmemCarveoutMaxShared));
-        eval_maps_kernel<true><<<grid, kEvThreads, smem, st>>>(maps14, N, gt_dense, boxes, box_count,
-                                                              max_boxes, gt_mode, up224, mask, inter_w,
-                                                              union_w, ciou);
-    } else {
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<false>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(eval_maps_kernel<false>,
-                                            cudaFuncAttributePreferredSharedMemoryCarveout,
-                                            (int)cudaSharedmemCarveoutMaxShared));
-        eval_maps_kernel<false><<<grid, kEvThreads, smem, st>>>(maps14, N, gt_dense, boxes, box_count,
-                                                               max_boxes, gt_mode, up224, mask, inter_w,
-                                                               union_w, ciou);
-    }
+        int per_sm = 0;                                        // persistent grid: every resident slot, once
+        AVT_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kEvThreads, smem));
+        if (per_sm < 1) per_sm = 1;
+        const int grid = N < sms * per_sm ? N : sms * per_sm;
+        kernel<<<grid, kEvThreads, smem, st>>>(maps14, N, gt_dense, boxes, box_count, max_boxes, gt_mode,
+                                               up224, mask, inter_w, union_w, ciou);
+        return AVT_OK;
+    };
+    const int rc = gt_dense ? launch(eval_maps_kernel<true>) : launch(eval_maps_kernel<false>);
+    if (rc != AVT_OK) return rc;
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
