@@ -17,6 +17,16 @@
 // sorted(pred)[k] == f(sorted(up)[k]) and {pred > thr or pred >= 1} is an up-set of `up`
 // whose boundary is located by searching the float key space with the very same f.
 #include "avt_common.cuh"
+#include <atomic>
+
+#ifndef AVT_EVAL_REGS
+#define AVT_EVAL_REGS 64
+#endif
+#ifdef AVT_EVAL_PLAIN_ST
+#define AVT_ST(p, v) (*(p) = (v))
+#else
+#define AVT_ST(p, v) __stcs((p), (v))
+#endif
 
 namespace avt {
 
@@ -28,7 +38,8 @@ constexpr int kEvThreads = 224;                  // 56 column quads x 4 row grou
 constexpr int kEvWarps = kEvThreads / 32;        // 7
 constexpr int kQuads = kDst / 4;                 // 56 column quads per row
 constexpr int kStrips = 28;                      // 8-row strips per column quad (2 edges + 13 x 2 halves)
-constexpr int kCap = 6144;                       // candidate keys kept for the exact refinement
+constexpr int kChunk = 128;                      // list entries a warp takes at a time (32 quads = one full row step)
+constexpr int kCap = 7168;                       // candidate keys kept for the exact refinement
 constexpr int kSampleSide = 56;                  // every 4th pixel in x and y
 constexpr int kNs = kSampleSide * kSampleSide;   // 3136 samples (14 per thread)
 constexpr int kSampPerThread = kNs / kEvThreads; // 14
@@ -39,6 +50,11 @@ constexpr int kMaxBoxesSmem = 32;
 // [0] maps that took the generic (bisection) selection, [1] maps evaluated -- dev statistics
 __device__ unsigned long long g_eval_stats[2];
 
+// Work tickets: maps are claimed one at a time (their cost varies, a static stride leaves a tail).
+// One slot per launch in flight, round robin; the last block out re-arms the slot.
+constexpr int kTicketSlots = 256;
+__device__ unsigned int g_eval_ticket[kTicketSlots][2];
+
 struct EvalSmem {
     float m[kSrc * kSrc];                        // the 14x14 map
     float rows[kSrc][kDst];                      // horizontally interpolated rows
@@ -48,6 +64,7 @@ struct EvalSmem {
     uint32_t bcast[4];
     uint32_t geo[kStrips];                       // packed strip geometry (strip_pack)
     int n_list;
+    int next_map;
     int16_t boxes[kMaxBoxesSmem][4];
 };
 
@@ -250,6 +267,26 @@ __device__ uint32_t select_generic(EvalSmem& S, uint32_t& kmin, uint32_t& kmax) 
     }
 }
 
+// Second-chance counting sweep for the few maps whose touching quads overflow the list: exact
+// per-pixel filter, only the pixels inside [tlo, thi) are appended (a few hundred).  One more
+// sweep instead of the generic bisection.  Returns this thread's #(u < tlo).
+__device__ __noinline__ uint32_t count_sweep_exact(EvalSmem& S, float tlo, float thi) {
+    uint32_t n_lt = 0;
+    for_each_row<1>(S, [](int, int) {}, [&](int, int, const float4& u) {
+        const float uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const bool below = uu[j] < tlo;
+            n_lt += below;
+            if (!below && uu[j] < thi) {
+                const int idx = atomicAdd(&S.n_list, 1);
+                if (idx < kCap) S.list[idx] = __float_as_uint(uu[j]);
+            }
+        }
+    });
+    return n_lt;
+}
+
 // f of the header comment: utils.py:234-239 applied to -u, then pred = 1 - h
 __device__ __forceinline__ float pred_of(float u, bool normalised, float vmin_h, float range) {
     float h = -u;
@@ -257,27 +294,29 @@ __device__ __forceinline__ float pred_of(float u, bool normalised, float vmin_h,
     return __fsub_rn(1.0f, h);
 }
 
-// One thread's strip: 4 pixels wide, 8 rows tall, between two source rows (see for_each_row).
+// One thread's strip: 4 pixels wide, 8 consecutive rows y0..y0+7 between source rows a and b
+// with weights w1 = w1_0 + r/16 on b and 1 - w1 on a (exact multiples of 1/32), which is tap()
+// written per strip.  Positions p = 4*j + rg, j = 0..6: p < 26 are the interior half-intervals
+// (source interval p >> 1, half p & 1 -- the half is rg & 1, so a thread's weights never change),
+// p = 26 / 27 are the clamped rows 0..7 / 216..223 (value = a*1 + b*0 on every row).
 struct Strip {
     float4 a, b;
-    int y0, ystep;
+    int y0;
     float w1_0, dw;
 };
 // Strip geometry is the same for every map: 28 packed words in shared memory, written once per
-// block.  bits 0-7 y0, bit 8 rows run downwards, bits 12-15 / 16-19 operand rows, bit 20 edge.
-__device__ __forceinline__ uint32_t strip_pack(int strip) {
-    const bool edge = (strip == 0 || strip == kStrips - 1);
-    const int s = (strip - 1) >> 1, half = (strip - 1) & 1;
-    const int ra = edge ? (strip ? kSrc - 1 : 0) : s + half;
-    const int rb = edge ? (strip ? kSrc - 1 : 1) : s + 1 - half;
-    const int y0 = edge ? (strip ? kDst - 8 : 0) : 16 * s + 8 + (half ? 15 : 0);
-    return (uint32_t)y0 | ((!edge && half) ? 0x100u : 0u) | ((uint32_t)ra << 12) | ((uint32_t)rb << 16) |
-           (edge ? 0x100000u : 0u);
+// block.  bits 0-7 y0, bits 12-15 / 16-19 operand rows, bit 20 edge, bit 21 second half.
+__device__ __forceinline__ uint32_t strip_pack(int p) {
+    const bool edge = p >= kStrips - 2;
+    const int s = p >> 1, half = p & 1;
+    const int ra = edge ? (half ? kSrc - 1 : 0) : s;
+    const int rb = edge ? (half ? kSrc - 1 : 1) : s + 1;
+    const int y0 = edge ? (half ? kDst - 8 : 0) : 16 * s + 8 + 8 * half;
+    return (uint32_t)y0 | ((uint32_t)ra << 12) | ((uint32_t)rb << 16) | (edge ? 0x100000u : 0u) |
+           ((!edge && half) ? 0x200000u : 0u);
 }
-__device__ __forceinline__ void strip_geometry(const EvalSmem& S, int j, int& y0, int& ystep) {
-    const uint32_t g = S.geo[4 * j + threadIdx.x / kQuads];
-    y0 = (int)(g & 0xffu);
-    ystep = 1 - (int)((g >> 7) & 2u);
+__device__ __forceinline__ int strip_y0(const EvalSmem& S, int j) {
+    return (int)(S.geo[4 * j + threadIdx.x / kQuads] & 0xffu);
 }
 __device__ __forceinline__ Strip strip_load(const EvalSmem& S, int j) {
     const int cq = threadIdx.x % kQuads;
@@ -286,10 +325,9 @@ __device__ __forceinline__ Strip strip_load(const EvalSmem& S, int j) {
     t.a = *reinterpret_cast<const float4*>(&S.rows[(g >> 12) & 15u][4 * cq]);
     t.b = *reinterpret_cast<const float4*>(&S.rows[(g >> 16) & 15u][4 * cq]);
     t.y0 = (int)(g & 0xffu);
-    t.ystep = 1 - (int)((g >> 7) & 2u);
     const bool edge = (g & 0x100000u) != 0u;
     t.dw = edge ? 0.0f : (1.0f / 16.0f);
-    t.w1_0 = edge ? 0.0f : (1.0f / 32.0f);
+    t.w1_0 = edge ? 0.0f : ((g & 0x200000u) ? (17.0f / 32.0f) : (1.0f / 32.0f));
     return t;
 }
 __device__ __forceinline__ float4 strip_row(const Strip& t, int r) {
@@ -326,15 +364,12 @@ __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int n
                                             uint32_t& inter, uint32_t& gsum, uint32_t& zc) {
     const int cq = threadIdx.x % kQuads;
     uint4 g = make_uint4(0, 0, 0, 0), gn = g;
+    // rows of a strip ascend, so every access of a half-strip is base + r * 224 elements: immediates
     auto request = [&](int k) -> uint4 {                        // GT words of half-strip k
-        int y0, ystep;
-        strip_geometry(S, k >> 1, y0, ystep);
-        const int ob = (y0 + (k & 1) * 4 * ystep) * kDst + 4 * cq, os = ystep * kDst;
+        const unsigned int* q = reinterpret_cast<const unsigned int*>(
+            gt_i + ((strip_y0(S, k >> 1) + (k & 1) * 4) * kDst + 4 * cq));
         uint4 d;
-        d.x = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + ob));
-        d.y = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (ob + os)));
-        d.z = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (ob + 2 * os)));
-        d.w = __ldcs(reinterpret_cast<const unsigned int*>(gt_i + (ob + 3 * os)));
+        d.x = __ldcs(q); d.y = __ldcs(q + kDst / 4); d.z = __ldcs(q + 2 * (kDst / 4)); d.w = __ldcs(q + 3 * (kDst / 4));
         return d;
     };
     if (kDenseGt) g = request(0);
@@ -343,21 +378,23 @@ __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int n
         if (kDenseGt && k + 1 < 2 * (kStrips / 4)) gn = request(k + 1);   // one half-strip ahead
         const Strip t = strip_load(S, k >> 1);
         const int h = (k & 1) * 4;
-        const int ob = (t.y0 + h * t.ystep) * kDst + 4 * cq, os = t.ystep * kDst;
-        const float w1_h = fmaf((float)h, t.dw, t.w1_0);
+        const int ob = (t.y0 + h) * kDst + 4 * cq;
+        float* const up_p = up_o + ob;
+        uint8_t* const mk_p = mk_o + ob;
+        float w1 = fmaf((float)h, t.dw, t.w1_0);
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            const float w1 = fmaf((float)r, t.dw, w1_h), w0 = 1.0f - w1;
+            const float w0 = 1.0f - w1;
             float4 u;
             u.x = lerp_rn(t.a.x, w0, t.b.x, w1); u.y = lerp_rn(t.a.y, w0, t.b.y, w1);
             u.z = lerp_rn(t.a.z, w0, t.b.z, w1); u.w = lerp_rn(t.a.w, w0, t.b.w, w1);
-            const int o = ob + r * os;
-            if (kUp) __stcs(reinterpret_cast<float4*>(up_o + o), u);
+            w1 += t.dw;
+            if (kUp) AVT_ST(reinterpret_cast<float4*>(up_p + r * kDst), u);
             const uint32_t m4 = (u.x >= t_on ? 1u : 0u) | (u.y >= t_on ? 0x100u : 0u) |
                                 (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
-            if (kMask) __stcs(reinterpret_cast<unsigned int*>(mk_o + o), m4);
+            if (kMask) AVT_ST(reinterpret_cast<unsigned int*>(mk_p + r * kDst), m4);
             const uint32_t gr = (r == 0) ? g.x : (r == 1) ? g.y : (r == 2) ? g.z : g.w;
-            const uint32_t g4 = kDenseGt ? gr : boxes_quad(S, nb, gt_mode, 4 * cq, t.y0 + (h + r) * t.ystep);
+            const uint32_t g4 = kDenseGt ? gr : boxes_quad(S, nb, gt_mode, 4 * cq, t.y0 + h + r);
             inter = __dp4a(m4, g4, inter);
             gsum = __dp4a(g4, 0x01010101u, gsum);
             zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
@@ -390,18 +427,22 @@ __device__ __noinline__ uint3 final_sweep_keys(const EvalSmem& S, uint32_t k_on,
 }
 
 template <bool kDenseGt>
-__global__ void __maxnreg__(48)
+__global__ void __maxnreg__(AVT_EVAL_REGS)
 eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restrict__ gt_dense,
                  const int16_t* __restrict__ boxes, const uint8_t* __restrict__ box_count,
                  int max_boxes, int gt_mode, float* __restrict__ up224, uint8_t* __restrict__ mask,
                  int32_t* __restrict__ inter_w, int32_t* __restrict__ union_w,
-                 double* __restrict__ ciou) {
+                 double* __restrict__ ciou, int slot) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EvalSmem& S = *reinterpret_cast<EvalSmem*>(smem_raw);
     const int tid = threadIdx.x;
     if (tid < kStrips) S.geo[tid] = strip_pack(tid);           // published by the first barrier below
+    unsigned int* ticket = g_eval_ticket[slot];
+    if (tid == 0) S.next_map = (int)atomicAdd(&ticket[0], 1u);
+    __syncthreads();
+    int map = S.next_map;
 
-    for (int map = blockIdx.x; map < N; map += gridDim.x) {
+    while (map < N) {
         // ---- load the map; source range and finiteness (one barrier pair)
         uint32_t bad = 0, kmn = 0xffffffffu, kmx = 0u;
         if (tid < kSrc * kSrc) {
@@ -417,8 +458,15 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
                 (&S.boxes[0][0])[tid] = boxes[((size_t)map * max_boxes) * 4 + tid];
         }
         for (int i = tid; i < 2 * kHist; i += kEvThreads) (&S.hist[0][0])[i] = 0u;
-        if (tid == 0) S.n_list = 0;
-        block_sum_min_max(S, bad, kmn, kmx);                     // also publishes S.m
+        if (tid == 0) { S.n_list = 0; S.next_map = (int)atomicAdd(&ticket[0], 1u); }   // claim one ahead
+        block_sum_min_max(S, bad, kmn, kmx);                     // also publishes S.m, S.next_map
+        const int next_map = S.next_map;
+        // the GT tile is not needed before the final sweep: ask L2 for it now (392 lines of 128 B)
+        if (kDenseGt && tid < kNpix / 256) {
+            const uint8_t* gp = gt_dense + (size_t)map * kNpix + tid * 256;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(gp));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(gp + 128));
+        }
         // ---- horizontal pass: rows[j][x] = m[j][sx0]*(1-wx) + m[j][sx1]*wx
         {
             int s0, s1; float w0, w1;
@@ -472,33 +520,68 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             const float ninf = __uint_as_float(0xff800000u), pinf = __uint_as_float(0x7f800000u);
             const float tlo = (sl == 0 || !(span2 > 0.0f)) ? ninf : lo2 + (float)(sl - 1) * inv2;
             const float thi = (sh == kHist - 1 || !(span2 > 0.0f)) ? pinf : lo2 + (float)sh * inv2;
-            // ---- counting sweep: quads entirely below the bracket are counted four at a time and
-            // quads entirely above cost nothing; the few lanes whose quad touches [tlo, thi) append
-            // it WHOLE (one shared atomic + one 16-byte store: no per-pixel work under divergence).
+            // ---- counting sweep: quads entirely below the bracket are counted four at a time,
+            // quads entirely above cost nothing, quads that touch [tlo, thi) are appended WHOLE to
+            // S.list.  The append is warp-convergent: one ballot per row, positions from the ballot,
+            // space taken from the shared list in 32-quad chunks per warp (one atomic per chunk),
+            // chunk tails padded with +Inf, which the post-pass ignores.
             uint32_t n_lt = 0;
             float fmn = pinf, fmx = ninf;
+            const int lane = tid & 31;
+            const uint32_t lt_mask = (1u << lane) - 1u;
+            int wpos = 0, wend = 0;                              // this warp's chunk (entries), uniform
+            auto pad_tail = [&]() {
+                const int i = wpos + 4 * lane;
+                if (i < wend && i + 4 <= kCap) *reinterpret_cast<float4*>(&S.list[i]) = make_float4(pinf, pinf, pinf, pinf);
+            };
 #pragma unroll 1
             for (int j = 0; j < kStrips / 4; ++j) {
                 const Strip t = strip_load(S, j);
+                float w1 = t.w1_0;
 #pragma unroll 4
                 for (int r = 0; r < 8; ++r) {
-                    const float4 u = strip_row(t, r);
+                    const float w0 = 1.0f - w1;
+                    float4 u;
+                    u.x = lerp_rn(t.a.x, w0, t.b.x, w1); u.y = lerp_rn(t.a.y, w0, t.b.y, w1);
+                    u.z = lerp_rn(t.a.z, w0, t.b.z, w1); u.w = lerp_rn(t.a.w, w0, t.b.w, w1);
+                    w1 += t.dw;
                     const float gmx = fmaxf(fmaxf(u.x, u.y), fmaxf(u.z, u.w));
                     const float gmn = fminf(fminf(u.x, u.y), fminf(u.z, u.w));
                     fmx = fmaxf(fmx, gmx); fmn = fminf(fmn, gmn);
-                    if (gmx < tlo) {
-                        n_lt += 4;
-                    } else if (gmn < thi) {
-                        const int p = atomicAdd(&S.n_list, 4);
-                        if (p + 4 <= kCap) *reinterpret_cast<float4*>(&S.list[p]) = u;
+                    const bool below = gmx < tlo;
+                    n_lt += below ? 4u : 0u;
+                    const bool touch = !below && gmn < thi;
+                    const uint32_t m = __ballot_sync(0xffffffffu, touch);
+                    if (m) {
+                        const int cnt = 4 * __popc(m);
+                        if (wpos + cnt > wend) {                 // uniform: take the next chunk
+                            pad_tail();
+                            int base = 0;
+                            if (lane == 0) base = atomicAdd(&S.n_list, kChunk);
+                            wpos = __shfl_sync(0xffffffffu, base, 0);
+                            wend = wpos + kChunk;
+                        }
+                        const int i = wpos + 4 * __popc(m & lt_mask);
+                        if (touch && i + 4 <= kCap) *reinterpret_cast<float4*>(&S.list[i]) = u;
+                        wpos += cnt;
                     }
                 }
             }
+            pad_tail();
             kmin = f2key(fmn); kmax = f2key(fmx);
             block_sum_min_max(S, n_lt, kmin, kmax);              // its barriers also publish the list
             // full-lane post-pass over the collected quads: keys in place, exact counts.  Float
             // order == key order except between -0 and +0, so a bracket edge at zero goes generic.
-            const int n = S.n_list;
+            int n = S.n_list;
+            if (n > kCap) {                                      // overflow: exact per-pixel retry
+                __syncthreads();
+                if (tid == 0) S.n_list = 0;
+                __syncthreads();
+                n_lt = count_sweep_exact(S, tlo, thi);
+                uint32_t z0 = 0, z1 = 0;
+                block_sum3(S, n_lt, z0, z1);
+                n = S.n_list;
+            }
             if (n <= kCap && tlo != 0.0f && thi != 0.0f) {
                 const uint32_t klo = f2key(tlo), khi = f2key(thi) - 1u;
                 uint32_t below = 0, inside = 0, unused = 0;
@@ -581,6 +664,11 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             union_w[map] = (int32_t)uni;
             ciou[map] = (double)inter / (double)uni;             // 0/0 -> NaN as numpy
         }
+        map = next_map;
+    }
+    if (tid == 0) {                                              // last block out re-arms the slot
+        __threadfence();
+        if (atomicAdd(&ticket[1], 1u) == gridDim.x - 1) { ticket[0] = 0u; ticket[1] = 0u; __threadfence(); }
     }
 }
 
@@ -746,8 +834,10 @@ extern "C" int avt_eval_maps(const float* maps14, int N, const uint8_t* gt_dense
         AVT_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kEvThreads, smem));
         if (per_sm < 1) per_sm = 1;
         const int grid = N < sms * per_sm ? N : sms * per_sm;
+        static std::atomic<unsigned int> launches{0};
+        const int slot = (int)(launches.fetch_add(1u) % (unsigned int)kTicketSlots);
         kernel<<<grid, kEvThreads, smem, st>>>(maps14, N, gt_dense, boxes, box_count, max_boxes, gt_mode,
-                                               up224, mask, inter_w, union_w, ciou);
+                                               up224, mask, inter_w, union_w, ciou, slot);
         return AVT_OK;
     };
     const int rc = gt_dense ? launch(eval_maps_kernel<true>) : launch(eval_maps_kernel<false>);

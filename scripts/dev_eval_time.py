@@ -6,6 +6,8 @@ sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 from audio_visual_tubes_b200 import _lib, evaluate_maps
+if os.environ.get('AVT_LIB_PATH'):
+    _lib.LIB_PATH = os.environ['AVT_LIB_PATH']
 from oracle import eval_oracle as eo
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 5158
