@@ -572,18 +572,18 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             block_sum_min_max(S, n_lt, kmin, kmax);              // its barriers also publish the list
             // full-lane post-pass over the collected quads: keys in place, exact counts.  Float
             // order == key order except between -0 and +0, so a bracket edge at zero goes generic.
-            int n = S.n_list;
-            if (n > kCap) {                                      // overflow: exact per-pixel retry
+            auto exact_sweep = [&](float lo_f, float hi_f) {     // one more sweep, per-pixel filter
                 __syncthreads();
                 if (tid == 0) S.n_list = 0;
                 __syncthreads();
-                n_lt = count_sweep_exact(S, tlo, thi);
+                n_lt = count_sweep_exact(S, lo_f, hi_f);
                 uint32_t z0 = 0, z1 = 0;
                 block_sum3(S, n_lt, z0, z1);
-                n = S.n_list;
-            }
-            if (n <= kCap && tlo != 0.0f && thi != 0.0f) {
-                const uint32_t klo = f2key(tlo), khi = f2key(thi) - 1u;
+            };
+            auto settle = [&](float lo_f, float hi_f) -> bool {  // keys in place, verify, select
+                const int n = S.n_list;
+                if (n > kCap || lo_f == 0.0f || hi_f == 0.0f) return false;
+                const uint32_t klo = f2key(lo_f), khi = f2key(hi_f) - 1u;
                 uint32_t below = 0, inside = 0, unused = 0;
                 for (int i = tid; i < n; i += kEvThreads) {
                     const uint32_t key = f2key(__uint_as_float(S.list[i]));
@@ -593,10 +593,22 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
                 }
                 block_sum3(S, below, inside, unused);
                 const uint32_t c_lt = n_lt + below;
-                if (c_lt <= (uint32_t)kRank && (uint32_t)kRank < c_lt + inside) {
-                    kstar = list_select(S, n, (uint32_t)kRank - c_lt, klo, khi);
-                    done = true;
-                }
+                if (!(c_lt <= (uint32_t)kRank && (uint32_t)kRank < c_lt + inside)) return false;
+                kstar = list_select(S, n, (uint32_t)kRank - c_lt, klo, khi);
+                return true;
+            };
+            if (S.n_list > kCap) exact_sweep(tlo, thi);          // too many touching quads
+            done = settle(tlo, thi);
+            if (!done) {
+                // the sampled bracket missed the rank (or sat on a zero edge): retry once with a
+                // 4x margin taken from the coarse histogram, exact filter; then the generic path
+                int bl2, bh2;
+                scan256(S.hist[0], (uint32_t)(kNs / 2 - 4 * kMargin), bl2, before);
+                scan256(S.hist[0], (uint32_t)(kNs / 2 + 4 * kMargin), bh2, before);
+                const float tlo2 = (bl2 == 0) ? ninf : smin + (float)bl2 * inv1;
+                const float thi2 = (bh2 == kHist - 1) ? pinf : smin + (float)(bh2 + 1) * inv1;
+                exact_sweep(tlo2, thi2);
+                done = settle(tlo2, thi2);
             }
         }
         if (!done) kstar = select_generic(S, kmin, kmax);
