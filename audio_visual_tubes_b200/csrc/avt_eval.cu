@@ -43,7 +43,10 @@ constexpr int kCap = 7168;                       // candidate keys kept for the 
 constexpr int kSampleSide = 56;                  // every 4th pixel in x and y
 constexpr int kNs = kSampleSide * kSampleSide;   // 3136 samples (14 per thread)
 constexpr int kSampPerThread = kNs / kEvThreads; // 14
-constexpr int kMargin = 24;                      // sample ranks either side of the median
+#ifndef AVT_EVAL_MARGIN
+#define AVT_EVAL_MARGIN 24
+#endif
+constexpr int kMargin = AVT_EVAL_MARGIN;                      // sample ranks either side of the median
 constexpr int kHist = 256;
 constexpr int kMaxBoxesSmem = 32;
 
