@@ -182,7 +182,7 @@ def run_reference(args):
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ----------------------------------------------------------------------------- GPU arm
@@ -364,7 +364,7 @@ def main():
             "clocks": clk.summary(),
             "also": also,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         # a captured graph holds NCCL work: tearing the communicator down under it can block, so
         # drain, meet the other ranks once more and leave without running destructors
@@ -466,5 +466,15 @@ def extras(avt, ev, _lib, cfg, dev, pk):
     return out
 
 
+def emit(line: dict):
+    """The ONE JSON line goes to the real stdout; everything else (NCCL banners, library chatter)
+    was re-routed to stderr at start-up."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)                      # fd 1 -> stderr for C libraries and stray prints
     main()
