@@ -58,6 +58,17 @@ __device__ unsigned long long g_eval_stats[2];
 constexpr int kTicketSlots = 256;
 __device__ unsigned int g_eval_ticket[kTicketSlots][2];
 
+// Thread -> (column quad, row group): a warp walks a 128-pixel row segment, so its global accesses
+// are 512 / 128 contiguous bytes.  (An 8-quad x 4-strip patch per warp crosses the median contour
+// on fewer row steps -- 71 % vs 86 % -- but measured slower: AVT_EVAL_PATCH_LANES keeps it around.)
+#ifndef AVT_EVAL_PATCH_LANES
+__device__ __forceinline__ int quad_col() { return threadIdx.x % kQuads; }
+__device__ __forceinline__ int row_group() { return threadIdx.x / kQuads; }
+#else
+__device__ __forceinline__ int quad_col() { return 8 * (threadIdx.x >> 5) + (threadIdx.x & 7); }
+__device__ __forceinline__ int row_group() { return (threadIdx.x >> 3) & 3; }
+#endif
+
 struct EvalSmem {
     float m[kSrc * kSrc];                        // the 14x14 map
     float rows[kSrc][kDst];                      // horizontally interpolated rows
@@ -192,7 +203,7 @@ __device__ uint32_t list_select(EvalSmem& S, int n, uint32_t r, uint32_t lo, uin
 // products and the same sum as tap()/lerp_rn, bit for bit.  Rows 0..7 and 216..223 clamp.
 template <int kUnroll, class StripFn, class RowFn>
 __device__ __forceinline__ void for_each_row(const EvalSmem& S, StripFn&& pre, RowFn&& fn) {
-    const int cq = threadIdx.x % kQuads, rg = threadIdx.x / kQuads;
+    const int cq = quad_col(), rg = row_group();
 #pragma unroll 1
     for (int j = 0; j < kStrips / 4; ++j) {
         const int strip = 4 * j + rg;
@@ -319,11 +330,11 @@ __device__ __forceinline__ uint32_t strip_pack(int p) {
            ((!edge && half) ? 0x200000u : 0u);
 }
 __device__ __forceinline__ int strip_y0(const EvalSmem& S, int j) {
-    return (int)(S.geo[4 * j + threadIdx.x / kQuads] & 0xffu);
+    return (int)(S.geo[4 * j + row_group()] & 0xffu);
 }
 __device__ __forceinline__ Strip strip_load(const EvalSmem& S, int j) {
-    const int cq = threadIdx.x % kQuads;
-    const uint32_t g = S.geo[4 * j + threadIdx.x / kQuads];
+    const int cq = quad_col();
+    const uint32_t g = S.geo[4 * j + row_group()];
     Strip t;
     t.a = *reinterpret_cast<const float4*>(&S.rows[(g >> 12) & 15u][4 * cq]);
     t.b = *reinterpret_cast<const float4*>(&S.rows[(g >> 16) & 15u][4 * cq]);
@@ -365,7 +376,7 @@ __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int n
                                             float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
                                             const uint8_t* __restrict__ gt_i,
                                             uint32_t& inter, uint32_t& gsum, uint32_t& zc) {
-    const int cq = threadIdx.x % kQuads;
+    const int cq = quad_col();
     uint4 g = make_uint4(0, 0, 0, 0), gn = g;
     // rows of a strip ascend, so every access of a half-strip is base + r * 224 elements: immediates
     auto request = [&](int k) -> uint4 {                        // GT words of half-strip k
@@ -412,7 +423,7 @@ template <bool kDenseGt>
 __device__ __noinline__ uint3 final_sweep_keys(const EvalSmem& S, uint32_t k_on, int nb, int gt_mode,
                                                float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
                                                const uint8_t* __restrict__ gt_i) {
-    const int cq = threadIdx.x % kQuads;
+    const int cq = quad_col();
     uint32_t inter = 0, gsum = 0, zc = 0;
     for_each_row<1>(S, [](int, int) {}, [&](int, int y, const float4& u) {
         const int o = y * kDst + 4 * cq;
@@ -531,7 +542,9 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             uint32_t n_lt = 0;
             float fmn = pinf, fmx = ninf;
             const int lane = tid & 31;
-            const uint32_t lt_mask = (1u << lane) - 1u;
+            uint32_t lt_mask = (1u << lane) - 1u;
+            uint32_t list_sa = (uint32_t)__cvta_generic_to_shared(&S.list[0]);
+            asm volatile("" : "+r"(lt_mask), "+r"(list_sa));   // keep both in registers (no rematerialisation)
             int wpos = 0, wend = 0;                              // this warp's chunk (entries), uniform
             auto pad_tail = [&]() {
                 const int i = wpos + 4 * lane;
@@ -562,10 +575,13 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
                             int base = 0;
                             if (lane == 0) base = atomicAdd(&S.n_list, kChunk);
                             wpos = __shfl_sync(0xffffffffu, base, 0);
+                            if (wpos + kChunk > kCap) wpos = 0;  // overflow (n_list says so): scribble on chunk 0
                             wend = wpos + kChunk;
                         }
-                        const int i = wpos + 4 * __popc(m & lt_mask);
-                        if (touch && i + 4 <= kCap) *reinterpret_cast<float4*>(&S.list[i]) = u;
+                        const uint32_t sa = list_sa + 4u * (uint32_t)(wpos + 4 * __popc(m & lt_mask));
+                        if (touch)
+                            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sa), "f"(u.x), "f"(u.y),
+                                         "f"(u.z), "f"(u.w) : "memory");
                         wpos += cnt;
                     }
                 }
