@@ -173,10 +173,20 @@ row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
         sp += w1; spa = fmaf(w1, a, spa);
         sn += w2; sna = fmaf(w2, a, sna);
     }
-    sp = block_sum_rg(sp, s_tmp);
-    spa = block_sum_rg(spa, s_tmp);
-    sn = block_sum_rg(sn, s_tmp);
-    sna = block_sum_rg(sna, s_tmp);
+    {   // four sums behind one pair of barriers
+        __shared__ float s_multi[kRowGradThreads / 32][4];
+        sp = warp_sum(sp); spa = warp_sum(spa); sn = warp_sum(sn); sna = warp_sum(sna);
+        if ((threadIdx.x & 31) == 0) {
+            const int w = threadIdx.x >> 5;
+            s_multi[w][0] = sp; s_multi[w][1] = spa; s_multi[w][2] = sn; s_multi[w][3] = sna;
+        }
+        __syncthreads();
+        sp = spa = sn = sna = 0.f;
+#pragma unroll
+        for (int i = 0; i < kRowGradThreads / 32; ++i) {
+            sp += s_multi[i][0]; spa += s_multi[i][1]; sn += s_multi[i][2]; sna += s_multi[i][3];
+        }
+    }
     const float sim1 = spa / sp, sim2 = sna / sn;
     for (int p = threadIdx.x; p < P; p += kRowGradThreads) {
         float a = A[(size_t)n * P + p];

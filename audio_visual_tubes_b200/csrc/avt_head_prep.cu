@@ -211,6 +211,7 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
                    float* __restrict__ loss_rows, float* __restrict__ loss_sum,
                    HeadScratch* scratch) {
     __shared__ float s_tmp[kRowThreads / 32];
+    __shared__ float s_multi[kRowThreads / 32][5];
     __shared__ bool s_last;
     const int n = blockIdx.x;
     const int L = N_a + 1 + (hp.use_neg ? 1 : 0);
@@ -234,11 +235,19 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
         sn += neg; sna = fmaf(neg, a, sna);
         spp = fmaf(pos, pos, spp);
     }
-    sp = block_sum(sp, s_tmp);
-    spa = block_sum(spa, s_tmp);
-    sn = block_sum(sn, s_tmp);
-    sna = block_sum(sna, s_tmp);
-    spp = block_sum(spp, s_tmp);
+    {   // five sums behind one pair of barriers (fixed order: deterministic)
+        sp = warp_sum(sp); spa = warp_sum(spa); sn = warp_sum(sn); sna = warp_sum(sna); spp = warp_sum(spp);
+        const int w = threadIdx.x >> 5;
+        if ((threadIdx.x & 31) == 0) {
+            s_multi[w][0] = sp; s_multi[w][1] = spa; s_multi[w][2] = sn; s_multi[w][3] = sna; s_multi[w][4] = spp;
+        }
+        __syncthreads();
+        sp = spa = sn = sna = spp = 0.f;
+#pragma unroll
+        for (int i = 0; i < kRowThreads / 32; ++i) {
+            sp += s_multi[i][0]; spa += s_multi[i][1]; sn += s_multi[i][2]; sna += s_multi[i][3]; spp += s_multi[i][4];
+        }
+    }
     const float l_first = (spa / sp) / hp.temp;
     const float l_last = (sna / sn) / hp.temp;
     if (weighted_A) {
@@ -253,18 +262,37 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
         lg[0] = l_first;
         if (hp.use_neg) lg[L - 1] = l_last;
     }
-    // log-sum-exp over the row; columns 1..N_a were written by the similarity kernel
-    float m = l_first;
-    if (hp.use_neg) m = fmaxf(m, l_last);
-    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) m = fmaxf(m, lg[j]);
-    m = block_max(m, s_tmp);
-    float s = 0.f;
-    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) s += expf(lg[j] - m);
+    // log-sum-exp over the row; columns 1..N_a were written by the similarity kernel.  One pass:
+    // every thread keeps a (max, sum of exp) pair, pairs are merged in a fixed order.
+    float m = -3.0e38f, s = 0.f;
     if (threadIdx.x == 0) {
-        s += expf(l_first - m);
-        if (hp.use_neg) s += expf(l_last - m);
+        m = l_first; s = 1.0f;
+        if (hp.use_neg) { const float mm = fmaxf(m, l_last); s = expf(m - mm) + expf(l_last - mm); m = mm; }
     }
-    s = block_sum(s, s_tmp);
+    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) {
+        const float x = lg[j];
+        const float mm = fmaxf(m, x);
+        s = s * expf(m - mm) + expf(x - mm);
+        m = mm;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float m2 = __shfl_xor_sync(0xffffffffu, m, o), s2 = __shfl_xor_sync(0xffffffffu, s, o);
+        const float mm = fmaxf(m, m2);
+        s = s * expf(m - mm) + s2 * expf(m2 - mm);
+        m = mm;
+    }
+    __syncthreads();                                         // s_multi is free again
+    if ((threadIdx.x & 31) == 0) { s_multi[threadIdx.x >> 5][0] = m; s_multi[threadIdx.x >> 5][1] = s; }
+    __syncthreads();
+    m = s_multi[0][0]; s = s_multi[0][1];
+#pragma unroll
+    for (int i = 1; i < kRowThreads / 32; ++i) {
+        const float m2 = s_multi[i][0], s2 = s_multi[i][1];
+        const float mm = fmaxf(m, m2);
+        s = s * expf(m - mm) + s2 * expf(m2 - mm);
+        m = mm;
+    }
     if (threadIdx.x == 0) loss_rows[n] = (m + logf(s)) - l_first;
 
     if (loss_sum == nullptr) return;
