@@ -68,12 +68,15 @@ constexpr int kPrepThreads = 512;
 constexpr int kPrepWarps = 16;
 constexpr int kPrepMaxCpw = 32;                  // channels per warp, C <= 512
 
-template <bool kWriteBf16>
+// kC / kP: compile-time C and P of the reference's shapes (512 channels, 14 x 14 positions) so that
+// every guard folds and every load / store offset is an immediate; 0 = take the run-time value.
+template <bool kWriteBf16, int kC, int kP>
 __global__ void __launch_bounds__(kPrepThreads, 2)
 prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
-                   const int32_t* __restrict__ pos_idx, int col_offset, int N_a, int C, int P,
+                   const int32_t* __restrict__ pos_idx, int col_offset, int N_a, int C_rt, int P_rt,
                    float* __restrict__ rnorm_v, float* __restrict__ A, float* __restrict__ msum,
                    __nv_bfloat16* __restrict__ vt, HeadScratch* scratch) {
+    const int C = kC ? kC : C_rt, P = kP ? kP : P_rt;
     extern __shared__ float smem[];
     float* s_a = smem;                       // [C]  positive audio row
     float* s_red = smem + C;                 // [3][kPrepWarps][32]
@@ -166,12 +169,13 @@ int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_id
     AVT_REQUIRE(C % 64 == 0 && C <= kPrepWarps * kPrepMaxCpw, "prep: C=%d must be a multiple of 64, <= 512", C);
     dim3 grid((P + 31) / 32, N_v);
     size_t smem = (size_t)(C + 3 * kPrepWarps * 32) * sizeof(float) + (vt_bf16 ? (size_t)32 * (C * 2 + 16) : 0);
-    if (vt_bf16)
-        prep_visual_kernel<true><<<grid, kPrepThreads, smem, st>>>(v, a_hat, pos_idx, col_offset, N_a,
-                                                                  C, P, rnorm_v, A, msum, vt_bf16, scratch);
-    else
-        prep_visual_kernel<false><<<grid, kPrepThreads, smem, st>>>(v, a_hat, pos_idx, col_offset, N_a,
-                                                                   C, P, rnorm_v, A, msum, nullptr, scratch);
+    const bool ref_shape = (C == 512 && P == 196);
+#define AVT_PREP(BF, KC, KP)                                                                        \
+    prep_visual_kernel<BF, KC, KP><<<grid, kPrepThreads, smem, st>>>(v, a_hat, pos_idx, col_offset, N_a, C, P, \
+                                                                     rnorm_v, A, msum, vt_bf16, scratch)
+    if (vt_bf16) { if (ref_shape) AVT_PREP(true, 512, 196); else AVT_PREP(true, 0, 0); }
+    else { if (ref_shape) AVT_PREP(false, 512, 196); else AVT_PREP(false, 0, 0); }
+#undef AVT_PREP
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
