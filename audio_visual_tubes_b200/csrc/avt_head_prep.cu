@@ -266,37 +266,18 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
         lg[0] = l_first;
         if (hp.use_neg) lg[L - 1] = l_last;
     }
-    // log-sum-exp over the row; columns 1..N_a were written by the similarity kernel.  One pass:
-    // every thread keeps a (max, sum of exp) pair, pairs are merged in a fixed order.
-    float m = -3.0e38f, s = 0.f;
+    // log-sum-exp over the row; columns 1..N_a were written by the similarity kernel
+    float m = l_first;
+    if (hp.use_neg) m = fmaxf(m, l_last);
+    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) m = fmaxf(m, lg[j]);
+    m = block_max(m, s_tmp);
+    float s = 0.f;
+    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) s += expf(lg[j] - m);
     if (threadIdx.x == 0) {
-        m = l_first; s = 1.0f;
-        if (hp.use_neg) { const float mm = fmaxf(m, l_last); s = expf(m - mm) + expf(l_last - mm); m = mm; }
+        s += expf(l_first - m);
+        if (hp.use_neg) s += expf(l_last - m);
     }
-    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) {
-        const float x = lg[j];
-        const float mm = fmaxf(m, x);
-        s = s * expf(m - mm) + expf(x - mm);
-        m = mm;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float m2 = __shfl_xor_sync(0xffffffffu, m, o), s2 = __shfl_xor_sync(0xffffffffu, s, o);
-        const float mm = fmaxf(m, m2);
-        s = s * expf(m - mm) + s2 * expf(m2 - mm);
-        m = mm;
-    }
-    __syncthreads();                                         // s_multi is free again
-    if ((threadIdx.x & 31) == 0) { s_multi[threadIdx.x >> 5][0] = m; s_multi[threadIdx.x >> 5][1] = s; }
-    __syncthreads();
-    m = s_multi[0][0]; s = s_multi[0][1];
-#pragma unroll
-    for (int i = 1; i < kRowThreads / 32; ++i) {
-        const float m2 = s_multi[i][0], s2 = s_multi[i][1];
-        const float mm = fmaxf(m, m2);
-        s = s * expf(m - mm) + s2 * expf(m2 - mm);
-        m = mm;
-    }
+    s = block_sum(s, s_tmp);
     if (threadIdx.x == 0) loss_rows[n] = (m + logf(s)) - l_first;
 
     if (loss_sum == nullptr) return;

@@ -204,6 +204,17 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         uint32_t tile = 0;
         for (int mt = mt0; mt < n_mt; mt += mt_step) {
             const int k = mt * kBM + row;
+            // per-(n, k) coefficients of the NEXT tile are requested while this one is swept, so
+            // their global-load latency never sits between the accumulator and the sweep
+            float nx_den = 1.0f, nx_sim = 0.f, nx_gs = 0.f;
+            auto fetch = [&](int n) {
+                if (kGrad && k < N_a && n < N_v) {
+                    nx_den = den[(size_t)n * N_a + k];
+                    nx_sim = sim[(size_t)n * N_a + k];
+                    nx_gs = gsim[(size_t)n * N_a + k];
+                }
+            };
+            fetch(g);
             for (int n = g; n < N_v; n += groups, ++tile) {
                 const uint32_t buf = tile & 1u, use = tile >> 1;
                 const int pos = pos_idx ? pos_idx[n] : col_offset + n;
@@ -212,11 +223,12 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 if (kGrad) {
                     float dnk = 1.0f;
                     if (k < N_a) {
-                        dnk = den[(size_t)n * N_a + k];
-                        cx.sm = sim[(size_t)n * N_a + k];
-                        cx.coef = gsim[(size_t)n * N_a + k] / dnk;
+                        dnk = nx_den;
+                        cx.sm = nx_sim;
+                        cx.coef = nx_gs / dnk;
                     }
                     exact = __any_sync(0xffffffffu, dnk < kTinyDen);
+                    fetch(n + groups);
                 }
                 __nv_bfloat16* gout = G + (size_t)n * P * n_a_pad + k;
                 const uint32_t pitch = (uint32_t)n_a_pad;

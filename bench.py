@@ -460,7 +460,23 @@ def extras(avt, ev, _lib, cfg, dev, pk):
             opt.step()
         ms = timed(train_step, 5, 2)
         out["train_cfg2_b128"] = {"clips_per_s": 128 / (ms * 1e-3), "ms_per_step": ms,
-                                  "note": "ResNet-18 backbones on stock PyTorch fp32 dominate; head is libavtubes"}
+                                  "note": "ResNet-18 backbones on stock PyTorch fp32 (as the reference runs them) dominate; head is libavtubes"}
+        try:                                                # same step, backbones under bf16 autocast
+            net = net.to(memory_format=torch.channels_last)
+            img_cl = img.contiguous(memory_format=torch.channels_last)
+            spec_cl = spec.contiguous(memory_format=torch.channels_last)
+
+            def train_step_amp():
+                opt.zero_grad(set_to_none=True)
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    loss = net.loss(img_cl, spec_cl)
+                loss.backward()
+                opt.step()
+            ms = timed(train_step_amp, 5, 2)
+            out["train_cfg2_b128_amp"] = {"clips_per_s": 128 / (ms * 1e-3), "ms_per_step": ms,
+                                          "note": "stock PyTorch backbones under bf16 autocast + channels_last; head unchanged (fp32 features in)"}
+        except Exception as e:
+            out["train_cfg2_b128_amp"] = {"error": repr(e)[:200]}
     except Exception as e:                                  # keep the headline line alive
         out["train_cfg2_b128"] = {"error": repr(e)[:200]}
     return out
