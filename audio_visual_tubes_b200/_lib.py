@@ -31,9 +31,9 @@ SIGNATURES = {
     "avt_audio_normalize": (_i, [_p, _i, _i, _p, _p, _p]),
     "avt_audio_normalize_backward": (_i, [_p, _p, _p, _i, _i, _p, _p]),
     "avt_head_workspace_bytes": (_z, [_i, _i, _i, _i, _i, _i]),
-    "avt_head_forward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i,
+    "avt_head_forward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
                               _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
-    "avt_head_backward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i,
+    "avt_head_backward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
                                _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _z, _p]),
     "avt_eval_maps": (_i, [_p, _i, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p]),
     "avt_eval_stats": (_i, [_p, _i]),

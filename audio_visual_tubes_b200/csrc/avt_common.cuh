@@ -116,14 +116,15 @@ int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_id
                        __nv_bfloat16* vt_bf16, HeadScratch* scratch, cudaStream_t st);
 int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int P, HeadParams hp,
                        float* Pos, float* Neg, float* weighted_A, float* logits,
-                       float* loss_rows, float* loss_sum, HeadScratch* scratch, cudaStream_t st);
+                       float* loss_rows, float* loss_sum, HeadScratch* scratch, const int32_t* pos_idx,
+                       int col_offset, const float* sim, int col_mult, cudaStream_t st);
 int launch_sim_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
 int launch_row_grad(const float* A, const float* logits, const float* loss_rows,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int P, HeadParams hp,
                     float dloss_scale, const float* dlogits, const float* dA, float* gsim, float* GA,
-                    cudaStream_t st);
+                    const float* sim, int col_mult, cudaStream_t st);
 int launch_bwd_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, const float* gsim,

@@ -63,7 +63,7 @@ extern "C" size_t avt_head_workspace_bytes(int N_v, int N_a, int C, int P, int p
 extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int N_a, int C, int P,
                                 const int32_t* pos_idx, int col_offset, float eps, float eps2,
                                 float tau, float temp, float mask_scale, int trimap, int use_neg,
-                                int precision, float* A, float* Pos, float* Neg, float* logits,
+                                int precision, int col_mult, float* A, float* Pos, float* Neg, float* logits,
                                 float* loss_rows, float* loss_sum, float* weighted_A,
                                 float* rnorm_v, float* sim, float* den, void* workspace,
                                 size_t workspace_bytes, void* stream) {
@@ -72,6 +72,9 @@ extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int
     AVT_REQUIRE(v && a_hat && A && Pos && Neg && logits && loss_rows && rnorm_v && sim && den,
                 "avt_head_forward: null pointer among required arguments");
     AVT_REQUIRE(tau > 0.f && temp > 0.f, "avt_head_forward: tau and temp must be positive");
+    AVT_REQUIRE(col_mult >= 1, "avt_head_forward: col_mult=%d must be >= 1", col_mult);
+    AVT_REQUIRE(col_mult == 1 || pos_idx != nullptr,
+                "avt_head_forward: tube mode (col_mult > 1) needs pos_idx (the audio row of every frame)");
     AVT_REQUIRE(workspace != nullptr, "avt_head_forward: workspace is null");
     // the forward regions lead both layouts, so a workspace sized for backward works too
     HeadWorkspace w = head_workspace_layout(N_v, N_a, C, P, precision, 0);
@@ -109,13 +112,13 @@ extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int
         if (rc != AVT_OK) return rc;
     }
     return launch_finish_rows(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A, logits, loss_rows,
-                              loss_sum, scratch, st);
+                              loss_sum, scratch, pos_idx, col_offset, sim, col_mult, st);
 }
 
 extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, int N_a, int C, int P,
                                  const int32_t* pos_idx, int col_offset, float eps, float eps2,
                                  float tau, float temp, float mask_scale, int trimap, int use_neg,
-                                 int precision, const float* A, const float* logits,
+                                 int precision, int col_mult, const float* A, const float* logits,
                                  const float* loss_rows, const float* rnorm_v, const float* sim,
                                  const float* den, float dloss_scale, const float* dlogits,
                                  const float* dA, float* dv, float* d_ahat, void* workspace,
@@ -125,6 +128,8 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
     AVT_REQUIRE(v && a_hat && A && logits && loss_rows && rnorm_v && sim && den && dv && d_ahat,
                 "avt_head_backward: null pointer among required arguments");
     AVT_REQUIRE(workspace != nullptr, "avt_head_backward: workspace is null");
+    AVT_REQUIRE(col_mult >= 1 && (col_mult == 1 || pos_idx != nullptr),
+                "avt_head_backward: col_mult=%d (tube mode needs pos_idx)", col_mult);
     HeadWorkspace w = head_workspace_layout(N_v, N_a, C, P, precision, 1);
     if (workspace_bytes < w.total) {
         set_error("avt_head_backward: workspace %zu B < required %zu B", workspace_bytes, w.total);
@@ -137,7 +142,7 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
     float* GA = reinterpret_cast<float*>(ws + w.ga);
 
     rc = launch_row_grad(A, logits, loss_rows, pos_idx, col_offset, N_v, N_a, P, hp, dloss_scale,
-                         dlogits, dA, gsim, GA, st);
+                         dlogits, dA, gsim, GA, sim, col_mult, st);
     if (rc != AVT_OK) return rc;
     AVT_CHECK_CUDA(cudaMemsetAsync(d_ahat, 0, (size_t)N_a * C * sizeof(float), st));
     if (precision == AVT_PRECISION_FP32) {

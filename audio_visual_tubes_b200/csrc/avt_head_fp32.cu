@@ -138,7 +138,8 @@ row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
                 const float* __restrict__ loss_rows, const int32_t* __restrict__ pos_idx,
                 int col_offset, int N_a, int P, HeadParams hp, float dloss_scale,
                 const float* __restrict__ dlogits, const float* __restrict__ dA,
-                float* __restrict__ gsim, float* __restrict__ GA) {
+                float* __restrict__ gsim, float* __restrict__ GA, const float* __restrict__ sim,
+                int col_mult) {
     __shared__ float s_tmp[kRowGradThreads / 32];
     const int n = blockIdx.x;
     const int L = N_a + 1 + (hp.use_neg ? 1 : 0);
@@ -147,11 +148,29 @@ row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
     const int pos = pos_idx ? pos_idx[n] : col_offset + n;
     const float itemp = 1.0f / hp.temp, itau = 1.0f / hp.tau;
 
-    for (int k = threadIdx.x; k < N_a; k += kRowGradThreads) {
-        float g = dloss_scale * expf(lg[1 + k] - lse);
-        if (dlogits) g += dlogits[(size_t)n * L + 1 + k];
-        float m = (k == pos) ? (1.0f - hp.mask_scale) : 1.0f;
-        gsim[(size_t)n * N_a + k] = g * m * itemp;
+    if (col_mult > 1) {
+        // tube mode: audio row k stands for T identical columns; d loss / d sim[n,k] sums their
+        // softmax weights, the masked copy (positive audio only) with its factor 1 - mask_scale.
+        // dlogits (if any) arrives already reduced over the copies WITH the mask factor applied.
+        const float tf = (float)col_mult;
+        for (int k = threadIdx.x; k < N_a; k += kRowGradThreads) {
+            float g;
+            if (k == pos) {
+                const float un = expf(sim[(size_t)n * N_a + k] * itemp - lse);
+                g = dloss_scale * ((tf - 1.0f) * un + (1.0f - hp.mask_scale) * expf(lg[1 + k] - lse));
+            } else {
+                g = dloss_scale * tf * expf(lg[1 + k] - lse);
+            }
+            if (dlogits) g += dlogits[(size_t)n * L + 1 + k];
+            gsim[(size_t)n * N_a + k] = g * itemp;
+        }
+    } else {
+        for (int k = threadIdx.x; k < N_a; k += kRowGradThreads) {
+            float g = dloss_scale * expf(lg[1 + k] - lse);
+            if (dlogits) g += dlogits[(size_t)n * L + 1 + k];
+            float m = (k == pos) ? (1.0f - hp.mask_scale) : 1.0f;
+            gsim[(size_t)n * N_a + k] = g * m * itemp;
+        }
     }
     float g1 = dloss_scale * (expf(lg[0] - lse) - 1.0f);
     if (dlogits) g1 += dlogits[(size_t)n * L];
@@ -204,10 +223,11 @@ row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
 int launch_row_grad(const float* A, const float* logits, const float* loss_rows,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int P, HeadParams hp,
                     float dloss_scale, const float* dlogits, const float* dA, float* gsim, float* GA,
-                    cudaStream_t st) {
+                    const float* sim, int col_mult, cudaStream_t st) {
     ProfScope _ps(kProfRowGrad, st);
     row_grad_kernel<<<N_v, kRowGradThreads, 0, st>>>(A, logits, loss_rows, pos_idx, col_offset, N_a,
-                                                     P, hp, dloss_scale, dlogits, dA, gsim, GA);
+                                                     P, hp, dloss_scale, dlogits, dA, gsim, GA, sim,
+                                                     col_mult);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }

@@ -213,7 +213,8 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
                    int P, HeadParams hp, float* __restrict__ Pos, float* __restrict__ Neg,
                    float* __restrict__ weighted_A, float* __restrict__ logits,
                    float* __restrict__ loss_rows, float* __restrict__ loss_sum,
-                   HeadScratch* scratch) {
+                   HeadScratch* scratch, const int32_t* __restrict__ pos_idx, int col_offset,
+                   const float* __restrict__ sim, int col_mult) {
     __shared__ float s_tmp[kRowThreads / 32];
     __shared__ float s_multi[kRowThreads / 32][5];
     __shared__ bool s_last;
@@ -266,16 +267,27 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
         lg[0] = l_first;
         if (hp.use_neg) lg[L - 1] = l_last;
     }
-    // log-sum-exp over the row; columns 1..N_a were written by the similarity kernel
+    // log-sum-exp over the row; columns 1..N_a were written by the similarity kernel.
+    // Tube mode (col_mult = T > 1, train_3D.py:129-130): audio row k stands for T identical
+    // logit columns, of which ONE -- in the row's positive audio -- carries the -99 mask
+    // (model.py:47,57).  Column k then weighs T (log T added to its logit); the positive audio
+    // contributes its masked logit once and its unmasked one T - 1 times.
+    const float log_t = (col_mult > 1) ? logf((float)col_mult) : 0.f;
+    const int posk = (col_mult > 1) ? (pos_idx ? pos_idx[n] : col_offset + n) : -1;
+    float y_pos_un = -3.0e38f;                               // unmasked logit of the positive audio
+    if (col_mult > 1 && posk >= 0 && posk < N_a)
+        y_pos_un = sim[(size_t)n * N_a + posk] / hp.temp + logf((float)(col_mult - 1));
     float m = l_first;
     if (hp.use_neg) m = fmaxf(m, l_last);
-    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) m = fmaxf(m, lg[j]);
+    m = fmaxf(m, y_pos_un);
+    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) m = fmaxf(m, lg[j] + ((j - 1 == posk) ? 0.f : log_t));
     m = block_max(m, s_tmp);
     float s = 0.f;
-    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) s += expf(lg[j] - m);
+    for (int j = 1 + threadIdx.x; j <= N_a; j += kRowThreads) s += expf(lg[j] + ((j - 1 == posk) ? 0.f : log_t) - m);
     if (threadIdx.x == 0) {
         s += expf(l_first - m);
         if (hp.use_neg) s += expf(l_last - m);
+        if (y_pos_un > -1.0e38f) s += expf(y_pos_un - m);
     }
     s = block_sum(s, s_tmp);
     if (threadIdx.x == 0) loss_rows[n] = (m + logf(s)) - l_first;
@@ -298,10 +310,12 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
 
 int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int P, HeadParams hp,
                        float* Pos, float* Neg, float* weighted_A, float* logits,
-                       float* loss_rows, float* loss_sum, HeadScratch* scratch, cudaStream_t st) {
+                       float* loss_rows, float* loss_sum, HeadScratch* scratch, const int32_t* pos_idx,
+                       int col_offset, const float* sim, int col_mult, cudaStream_t st) {
     ProfScope _ps(kProfFinish, st);
     finish_rows_kernel<<<N_v, kRowThreads, 0, st>>>(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A,
-                                                    logits, loss_rows, loss_sum, scratch);
+                                                    logits, loss_rows, loss_sum, scratch, pos_idx,
+                                                    col_offset, sim, col_mult);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }

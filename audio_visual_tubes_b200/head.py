@@ -59,9 +59,11 @@ def audio_normalize_backward(a_hat, rnorm_a, d_ahat):
 
 
 def head_forward_raw(v, a_hat, cfg: HeadConfig, pos_idx=None, col_offset=0, want_weighted=False,
-                     for_backward=False):
+                     for_backward=False, col_mult=1):
     """One ``avt_head_forward`` call.  ``a_hat`` must already be L2-normalised rows.
-    Returns a dict of output tensors (+ the workspace to hand to the backward)."""
+    Returns a dict of output tensors (+ the workspace to hand to the backward).
+    ``col_mult = T > 1``: tube mode, ``a_hat`` holds the DISTINCT audio rows, each standing for T
+    identical logit columns (see include/avtubes.h); ``logits`` is then the compact row."""
     _lib.require_cuda(v, a_hat)
     lib = _lib.load()
     assert v.dtype == torch.float32 and a_hat.dtype == torch.float32
@@ -86,13 +88,14 @@ def head_forward_raw(v, a_hat, cfg: HeadConfig, pos_idx=None, col_offset=0, want
         rc = lib.avt_head_forward(
             _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(pos_idx), int(col_offset),
             cfg.eps, cfg.eps2, cfg.tau, cfg.temp, cfg.mask_scale, int(cfg.trimap), int(cfg.use_neg),
-            prec, _lib.ptr(out["A"]), _lib.ptr(out["Pos"]), _lib.ptr(out["Neg"]),
+            prec, int(col_mult), _lib.ptr(out["A"]), _lib.ptr(out["Pos"]), _lib.ptr(out["Neg"]),
             _lib.ptr(out["logits"]), _lib.ptr(out["loss_rows"]), _lib.ptr(out["loss_sum"]),
             _lib.ptr(out["weighted_A"]), _lib.ptr(out["rnorm_v"]), _lib.ptr(out["sim"]),
             _lib.ptr(out["den"]), _lib.ptr(ws), C.c_size_t(nbytes), _lib.stream_ptr())
     _lib.check(rc, "avt_head_forward")
     out["workspace"] = ws
     out["pos_idx"] = pos_idx
+    out["col_mult"] = int(col_mult)
     return out
 
 
@@ -117,12 +120,49 @@ def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits
         rc = lib.avt_head_backward(
             _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(saved["pos_idx"]), int(col_offset),
             cfg.eps, cfg.eps2, cfg.tau, cfg.temp, cfg.mask_scale, int(cfg.trimap), int(cfg.use_neg),
-            prec, _lib.ptr(saved["A"]), _lib.ptr(saved["logits"]), _lib.ptr(saved["loss_rows"]),
+            prec, int(saved.get("col_mult", 1)), _lib.ptr(saved["A"]), _lib.ptr(saved["logits"]),
+            _lib.ptr(saved["loss_rows"]),
             _lib.ptr(saved["rnorm_v"]), _lib.ptr(saved["sim"]), _lib.ptr(saved["den"]),
             float(dloss_scale), _lib.ptr(dlogits), _lib.ptr(dA), _lib.ptr(dv), _lib.ptr(d_ahat),
             _lib.ptr(ws), C.c_size_t(ws.numel()), _lib.stream_ptr())
     _lib.check(rc, "avt_head_backward")
     return dv, d_ahat
+
+
+def tube_positions(n_v: int, col_mult: int, device, row_offset: int = 0):
+    """(audio row, copy) of every frame under the reference's ``(b t)`` flattening
+    (model.py:49) with each spectrogram repeated T times (train_3D.py:129-130): frame n belongs
+    to clip n // T and is masked against copy n % T of that clip's audio."""
+    rows = torch.arange(row_offset, row_offset + n_v, device=device)
+    return (rows // col_mult).int(), (rows % col_mult).long()
+
+
+def expand_tube_logits(out, cfg: HeadConfig, copy_idx):
+    """Compact logits of tube mode -> the reference's ``[N_v, N_a*T + 1(+1)]`` row
+    (model.py:56-59): every audio column T times, the frame's own copy carrying the mask."""
+    T = out["col_mult"]
+    lg, sim, pos = out["logits"], out["sim"], out["pos_idx"].long()
+    n_v, n_a = sim.shape
+    mid = (sim / cfg.temp).repeat_interleave(T, dim=1)
+    rows = torch.arange(n_v, device=lg.device)
+    ok = (pos >= 0) & (pos < n_a)
+    mid[rows[ok], pos[ok] * T + copy_idx[ok]] = lg[rows[ok], 1 + pos[ok]]
+    parts = [lg[:, :1], mid] + ([lg[:, -1:]] if cfg.use_neg else [])
+    return torch.cat(parts, dim=1)
+
+
+def reduce_tube_dlogits(g_full, out, cfg: HeadConfig, copy_idx):
+    """Adjoint of ``expand_tube_logits`` for the kernels: per audio row the sum over its T copies
+    of d/dlogit * d logit/d sim-scaled, i.e. with the mask factor of the masked copy applied."""
+    T = out["col_mult"]
+    n_v, n_a = out["sim"].shape
+    pos = out["pos_idx"].long()
+    mid = g_full[:, 1:1 + n_a * T].reshape(n_v, n_a, T).clone()
+    rows = torch.arange(n_v, device=g_full.device)
+    ok = (pos >= 0) & (pos < n_a)
+    mid[rows[ok], pos[ok], copy_idx[ok]] *= (1.0 - cfg.mask_scale)
+    parts = [g_full[:, :1], mid.sum(dim=2)] + ([g_full[:, -1:]] if cfg.use_neg else [])
+    return torch.cat(parts, dim=1).contiguous()
 
 
 class _HardWayHead(torch.autograd.Function):
@@ -134,17 +174,21 @@ class _HardWayHead(torch.autograd.Function):
     (no reference training script back-propagates through them)."""
 
     @staticmethod
-    def forward(ctx, v, a, cfg, pos_idx, col_offset, want_weighted):
+    def forward(ctx, v, a, cfg, pos_idx, col_offset, want_weighted, col_mult=1, copy_idx=None):
         need_grad = v.requires_grad or a.requires_grad
         v = v.contiguous().float()
         a_hat, rn_a = audio_normalize(a)
-        out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, want_weighted, for_backward=need_grad)
+        out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, want_weighted, for_backward=need_grad,
+                               col_mult=col_mult)
         ctx.cfg, ctx.col_offset = cfg, col_offset
         ctx.saved = out
+        ctx.copy_idx = copy_idx
         ctx.save_for_backward(v, a_hat, rn_a)
         w = out["weighted_A"] if want_weighted else out["A"].new_empty(0)
         ctx.mark_non_differentiable(out["Pos"], out["Neg"], w)
-        return out["A"], out["logits"], out["Pos"], out["Neg"], w, out["loss_rows"]
+        logits = out["logits"] if col_mult == 1 else expand_tube_logits(out, cfg, copy_idx)
+        ctx.logits_full = logits
+        return out["A"], logits, out["Pos"], out["Neg"], w, out["loss_rows"]
 
     @staticmethod
     def backward(ctx, gA, glogits, gPos, gNeg, gW, gloss_rows):
@@ -155,15 +199,17 @@ class _HardWayHead(torch.autograd.Function):
         scale = 0.0
         if gloss_rows is not None:
             g = gloss_rows.contiguous().float()
-            lg = ctx.saved["logits"]
+            lg = ctx.logits_full
             sm = torch.softmax(lg, dim=1)
             sm[:, 0] -= 1.0
             extra = sm * g[:, None]
             dlogits = extra if dlogits is None else dlogits + extra
+        if dlogits is not None and ctx.saved["col_mult"] > 1:
+            dlogits = reduce_tube_dlogits(dlogits.contiguous().float(), ctx.saved, ctx.cfg, ctx.copy_idx)
         dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, scale, dlogits, gA,
                                        ctx.col_offset)
         da = audio_normalize_backward(a_hat, rn_a, d_ahat)
-        return dv, da, None, None, None, None
+        return dv, da, None, None, None, None, None, None
 
 
 class _HardWayLoss(torch.autograd.Function):
@@ -171,11 +217,12 @@ class _HardWayLoss(torch.autograd.Function):
     is one scalar, so the backward needs no dlogits tensor at all."""
 
     @staticmethod
-    def forward(ctx, v, a, cfg, pos_idx, col_offset, divisor):
+    def forward(ctx, v, a, cfg, pos_idx, col_offset, divisor, col_mult=1):
         need_grad = v.requires_grad or a.requires_grad
         v = v.contiguous().float()
         a_hat, rn_a = audio_normalize(a)
-        out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=need_grad)
+        out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=need_grad,
+                               col_mult=col_mult)
         ctx.cfg, ctx.col_offset, ctx.divisor = cfg, col_offset, divisor
         ctx.saved = out
         ctx.save_for_backward(v, a_hat, rn_a)
@@ -188,26 +235,40 @@ class _HardWayLoss(torch.autograd.Function):
         scale = float(gloss) / ctx.divisor
         dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, scale, None, None, ctx.col_offset)
         da = audio_normalize_backward(a_hat, rn_a, d_ahat)
-        return dv, da, None, None, None, None
+        return dv, da, None, None, None, None, None
 
 
 def hardway_head(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0,
-                 return_weighted=False):
+                 return_weighted=False, col_mult=1):
     """v [N_v,C,P] (or [N_v,C,H,W]), a [N_a,C] -> (A [N_v,P], logits [N_v,N_a+1(+1)], Pos, Neg,
-    weighted_A or None, loss_rows [N_v])."""
+    weighted_A or None, loss_rows [N_v]).
+
+    ``col_mult = T > 1`` (tube mode): ``a`` holds the N_v / T DISTINCT audio rows of clips whose T
+    frames are consecutive rows of ``v``; the result is what the reference computes after
+    repeating every spectrogram T times (train_3D.py:129-130) -- logits ``[N_v, N_a*T + 1(+1)]``
+    included -- at 1/T of the similarity work, and ``a.grad`` is the gradient wrt the distinct
+    rows (the sum over the copies)."""
     if v.dim() == 4:
         v = v.flatten(2)
+    copy_idx = None
+    if col_mult > 1:
+        auto_pos, copy_idx = tube_positions(v.shape[0], col_mult, v.device, col_offset)
+        pos_idx = auto_pos if pos_idx is None else pos_idx
     A, logits, Pos, Neg, w, loss_rows = _HardWayHead.apply(v, a, cfg, pos_idx, col_offset,
-                                                           return_weighted)
+                                                           return_weighted, col_mult, copy_idx)
     return A, logits, Pos, Neg, (w if return_weighted else None), loss_rows
 
 
-def hardway_loss(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0, divisor=None):
+def hardway_loss(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0, divisor=None,
+                 col_mult=1):
     """Fused ``CrossEntropyLoss()(logits, zeros)`` of the head (``train_hardway_1frame.py:130-131``):
-    mean over the N_v rows (or sum / divisor for row-sharded ranks)."""
+    mean over the N_v rows (or sum / divisor for row-sharded ranks).  ``col_mult``: tube mode, see
+    ``hardway_head``."""
     if v.dim() == 4:
         v = v.flatten(2)
-    return _HardWayLoss.apply(v, a, cfg, pos_idx, col_offset, float(divisor or v.shape[0]))
+    if col_mult > 1 and pos_idx is None:
+        pos_idx, _ = tube_positions(v.shape[0], col_mult, v.device, col_offset)
+    return _HardWayLoss.apply(v, a, cfg, pos_idx, col_offset, float(divisor or v.shape[0]), col_mult)
 
 
 def hardway_value_and_grad(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0,

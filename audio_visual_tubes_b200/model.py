@@ -72,7 +72,11 @@ class HardWayAttention(nn.Module):
     """model.py:38-60.  ``audio_features [N_a,512]`` (any scale: the head re-normalises, which
     is the identity on the reference's already-normalised rows), ``video_features
     [b,512,T,14,14]``.  ``N_a == 1`` broadcasts against the b*T frames exactly like the
-    reference's einsum does at test time (train_3D.py:153-154)."""
+    reference's einsum does at test time (train_3D.py:153-154).  ``N_a == b`` with T > 1 is the
+    de-duplicated tube mode: pass the b distinct clip embeddings instead of
+    repeating each T times (train_3D.py:129-130) and get the same ``(A, logits)`` -- logits
+    ``[(bT), (bT)+2]`` -- at 1/T of the similarity flops (and run the audio backbone on b
+    spectrograms instead of bT)."""
 
     def __init__(self, precision: str = "bf16"):
         super().__init__()
@@ -87,7 +91,8 @@ class HardWayAttention(nn.Module):
         if aud.shape[0] == 1 and n > 1:
             aud = aud.expand(n, -1)
         cfg = HeadConfig(eps=self.epsilon, eps2=self.epsilon2, tau=self.tau, precision=self.precision)
-        A, logits, _, _, _, _ = hardway_head(v.contiguous(), aud.contiguous(), cfg)
+        col_mult = t if (aud.shape[0] == b and t > 1 and b > 1) else 1
+        A, logits, _, _, _, _ = hardway_head(v.contiguous(), aud.contiguous(), cfg, col_mult=col_mult)
         return A.view(n, 1, h, w), logits
 
 

@@ -94,14 +94,26 @@ int avt_audio_normalize_backward(const float* a_hat, const float* rnorm_a,
  *   loss_sum     [1] or NULL     sum_n loss_rows[n] (deterministic order)
  *   weighted_A   [N_v, P] or NULL model.py:148-152
  * Saved for backward (all required)
- *   rnorm_v [N_v, P], sim [N_v, N_a] (pooled, before mask), den [N_v, N_a] */
+ *   rnorm_v [N_v, P], sim [N_v, N_a] (pooled, before mask), den [N_v, N_a]
+ *
+ * Tube mode, col_mult = T > 1 (train_3D.py:129-130, train_hardway.py:128-129
+ * repeat every spectrogram T times, so model.py:47-51 scores (bT)^2 cells of which only
+ * b*(bT) are distinct): pass the b DISTINCT audio rows (N_a = b), pos_idx[n] = the audio row of
+ * frame n (required), and col_mult = T.  Audio row k then stands for T identical logit columns;
+ * exactly one of them, in the row's positive audio, carries the 1 - mask_scale factor of
+ * model.py:47,57.  loss_rows / loss_sum are those of the reference's [N_v, N_a*T + 2] logits;
+ * `logits` holds the COMPACT row [sim1, N_a masked-as-usual columns, sim2] (the host mirror
+ * expands it), and d_ahat of the backward is the gradient wrt the distinct rows (the sum over
+ * the copies, what autograd gives through `repeat`).  dlogits, if given in tube mode, is
+ * compact too: per audio row the sum over its T copies with the mask factor already applied.
+ * 1/T of the similarity flops, 1/T of the audio-backbone work upstream. */
 size_t avt_head_workspace_bytes(int N_v, int N_a, int C, int P, int precision, int backward);
 
 int avt_head_forward(const float* v, const float* a_hat,
                      int N_v, int N_a, int C, int P,
                      const int32_t* pos_idx, int col_offset,
                      float eps, float eps2, float tau, float temp, float mask_scale,
-                     int trimap, int use_neg, int precision,
+                     int trimap, int use_neg, int precision, int col_mult,
                      float* A, float* Pos, float* Neg, float* logits,
                      float* loss_rows, float* loss_sum, float* weighted_A,
                      float* rnorm_v, float* sim, float* den,
@@ -117,7 +129,7 @@ int avt_head_backward(const float* v, const float* a_hat,
                       int N_v, int N_a, int C, int P,
                       const int32_t* pos_idx, int col_offset,
                       float eps, float eps2, float tau, float temp, float mask_scale,
-                      int trimap, int use_neg, int precision,
+                      int trimap, int use_neg, int precision, int col_mult,
                       const float* A, const float* logits, const float* loss_rows,
                       const float* rnorm_v, const float* sim, const float* den,
                       float dloss_scale, const float* dlogits, const float* dA,

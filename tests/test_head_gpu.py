@@ -154,10 +154,56 @@ def test_tube_mode_and_broadcast(precision):
     assert A.shape == (n, 1, 14, 14) and logits.shape == (n, n + 2)
     assert rel(A.cpu().numpy().reshape(n, -1), HEAD["tube_b2t4/A"].reshape(n, -1)) < tol
     assert rel(logits.cpu().numpy(), HEAD["tube_b2t4/logits"]) < tol
+    # de-duplicated tube mode: the b DISTINCT embeddings instead of T copies of each -- same
+    # outputs as the unmodified reference's golden vectors, 1/T of the similarity work
+    A2, l2 = att(torch.tensor(a, device="cuda"), vid)
+    assert A2.shape == (n, 1, 14, 14) and l2.shape == (n, n + 2)
+    assert rel(A2.cpu().numpy().reshape(n, -1), HEAD["tube_b2t4/A"].reshape(n, -1)) < tol
+    assert rel(l2.cpu().numpy(), HEAD["tube_b2t4/logits"]) < tol
     # test time: one audio row against T frames (train_3D.py:153-154)
     A1, l1 = att(torch.tensor(a[:1], device="cuda"), vid[:1])
     assert rel(l1.cpu().numpy(), HEAD["tube_b2t4/logits_bcast"]) < tol
     assert rel(A1.cpu().numpy().reshape(t, -1), HEAD["tube_b2t4/A_bcast"].reshape(t, -1)) < tol
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("b,t", [(3, 4), (5, 16), (9, 2)])
+def test_tube_dedup_forward_backward(b, t, precision):
+    """col_mult = T: distinct audio rows against (b T) frames == the head on T copies of every row
+    (train_3D.py:129-130, model.py:47-59): logits, per-row loss, dv, and the audio gradient summed
+    over the copies -- through logits, through A and through the fused per-row loss."""
+    from audio_visual_tubes_b200 import HeadConfig, hardway_head, hardway_loss
+    n = b * t
+    v, a = head_features(n, b, 40 + b, "mix")
+    rng = np.random.default_rng(b * 100 + t)
+    dlog = (rng.standard_normal((n, n + 2)) * 1e-2).astype(np.float32)
+    dA = (rng.standard_normal((n, 196)) * 1e-3).astype(np.float32)
+    a_full = np.repeat(a, t, axis=0)
+    o, dv_o, da_o = ho.head_forward_backward_torch(v, a_full, dlogits=dlog, dA=dA, loss_scale=0.7)
+    da_o = da_o.reshape(b, t, -1).sum(1)
+    tol, gtol = TOL[precision]
+    cfg = HeadConfig(precision=precision)
+    vt = torch.tensor(v, device="cuda", requires_grad=True)
+    at = torch.tensor(a, device="cuda", requires_grad=True)
+    A, logits, Pos, Neg, _, loss_rows = hardway_head(vt, at, cfg, col_mult=t)
+    assert logits.shape == (n, n + 2)
+    assert rel(logits.detach().cpu().numpy(), o["logits"]) < tol
+    assert rel(A.detach().cpu().numpy(), o["A"]) < tol
+    assert rel(loss_rows.detach().cpu().numpy(), o["loss_rows"]) < 5 * tol
+    total = 0.7 * loss_rows.mean() + (torch.tensor(dlog, device="cuda") * logits).sum() + \
+        (torch.tensor(dA, device="cuda") * A).sum()
+    total.backward()
+    assert relnorm(vt.grad.cpu().numpy(), dv_o) < gtol
+    assert relnorm(at.grad.cpu().numpy(), da_o) < gtol
+    # fused loss path: the kernels see only dloss_scale
+    o2, dv2, da2 = ho.head_forward_backward_torch(v, a_full)
+    v2 = torch.tensor(v, device="cuda", requires_grad=True)
+    a2 = torch.tensor(a, device="cuda", requires_grad=True)
+    loss = hardway_loss(v2, a2, cfg, col_mult=t)
+    loss.backward()
+    assert abs(float(loss.detach()) - o2["loss"]) < 5 * tol * max(1.0, abs(o2["loss"]))
+    assert relnorm(v2.grad.cpu().numpy(), dv2) < gtol
+    assert relnorm(a2.grad.cpu().numpy(), da2.reshape(b, t, -1).sum(1)) < gtol
 
 
 @pytest.mark.parametrize("precision", PRECISIONS)
