@@ -272,19 +272,22 @@ def hardway_loss(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=
 
 
 def hardway_value_and_grad(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0,
-                           divisor=None, want_grad=True):
+                           divisor=None, want_grad=True, col_mult=1):
     """One training step of the head without autograd bookkeeping: returns
     ``(loss [1] device tensor, dv [N_v,C,P], da [N_a,C])`` for
     ``loss = sum_n CE(logits[n], 0) / divisor`` (divisor defaults to N_v: the reference's
     ``CrossEntropyLoss`` mean, train_hardway_1frame.py:130-133).  Everything is enqueued on the
-    current stream; nothing synchronises."""
+    current stream; nothing synchronises.  ``col_mult``: tube mode, see ``hardway_head``."""
     _lib.require_cuda(v, a)
     if v.dim() == 4:
         v = v.flatten(2)
     v = v.contiguous().float()
     divisor = float(divisor or v.shape[0])
+    if col_mult > 1 and pos_idx is None:
+        pos_idx, _ = tube_positions(v.shape[0], col_mult, v.device, col_offset)
     a_hat, rn_a = audio_normalize(a)
-    out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=want_grad)
+    out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=want_grad,
+                           col_mult=col_mult)
     loss = out["loss_sum"] / divisor
     if not want_grad:
         return loss, None, None

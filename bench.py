@@ -443,6 +443,29 @@ def extras(avt, ev, _lib, cfg, dev, pk):
                              "fwd_hbm_gbs": bytes_alg / (fwd_ms * 1e-3) / 1e9,
                              "fwd_hbm_frac": bytes_alg / (fwd_ms * 1e-3) / 1e9 / pk["hbm"]}
 
+    # config 4: tube model, b = 64 clips x T = 16 frames = 1024 frames.  Reference-faithful mode scores
+    # every frame against the 1024 REPEATED audio rows (train_3D.py:129-130); tube mode scores it
+    # against the 64 distinct ones with column multiplicity 16 -- same logits, loss and gradients.
+    try:
+        bt, T = 64, 16
+        g4 = torch.Generator(device=dev).manual_seed(4)
+        v4 = torch.randn(bt * T, C, P, device=dev, generator=g4).abs_()
+        a4 = torch.randn(bt, C, device=dev, generator=g4).abs_()
+        a4_rep = a4.repeat_interleave(T, dim=0).contiguous()
+        ms_rep = timed(lambda: avt.hardway_value_and_grad(v4, a4_rep, cfg), 10, 3)
+        ms_ded = timed(lambda: avt.hardway_value_and_grad(v4, a4, cfg, col_mult=T), 10, 3)
+        l_rep = float(avt.hardway_value_and_grad(v4, a4_rep, cfg, want_grad=False)[0][0])
+        l_ded = float(avt.hardway_value_and_grad(v4, a4, cfg, col_mult=T, want_grad=False)[0][0])
+        cells4 = (bt * T) * (bt * T) * P
+        out["tube_cfg4"] = {"frames": bt * T, "T": T, "reference_cells": cells4, "unique_cells": cells4 // T,
+                            "repeated_audio": {"ms_fwd_bwd": ms_rep, "cells_per_s": cells4 / (ms_rep * 1e-3), "loss": l_rep},
+                            "tube_mode": {"ms_fwd_bwd": ms_ded, "reference_cells_per_s": cells4 / (ms_ded * 1e-3),
+                                          "unique_cells_per_s": cells4 / T / (ms_ded * 1e-3), "loss": l_ded},
+                            "speedup": ms_rep / ms_ded}
+        del v4, a4, a4_rep
+    except Exception as e:
+        out["tube_cfg4"] = {"error": repr(e)[:200]}
+
     # whole training step, config 2: stock-PyTorch backbones + fused head + Adam
     try:
         import types
