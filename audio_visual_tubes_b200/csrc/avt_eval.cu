@@ -49,6 +49,7 @@ constexpr int kSampPerThread = kNs / kEvThreads; // 14
 constexpr int kMargin = AVT_EVAL_MARGIN;                      // sample ranks either side of the median
 constexpr int kHist = 256;
 constexpr int kMaxBoxesSmem = 32;
+static_assert(kEvThreads == kDst, "rasterise_planes: one thread per destination row");
 
 // [0] maps that took the generic (bisection) selection, [1] maps evaluated -- dev statistics
 __device__ unsigned long long g_eval_stats[2];
@@ -352,6 +353,38 @@ __device__ __forceinline__ float4 strip_row(const Strip& t, int r) {
     return u;
 }
 
+// Box ground truth as two bit planes in the (by then idle) candidate list: plane 0 = covered by
+// at least one box, plane 1 = by at least two (utils.py:264-273 needs the union, :243-262 the
+// count clipped at two annotators).  Thread y rasterises row y: 7 words per plane.
+constexpr int kPlaneWords = kDst * (kDst / 32);   // 1568
+__device__ __forceinline__ void rasterise_planes(EvalSmem& S, int nb) {
+    const int y = threadIdx.x;                     // kEvThreads == kDst
+#pragma unroll
+    for (int w = 0; w < kDst / 32; ++w) {
+        uint32_t c0 = 0, c1 = 0;
+        for (int q = 0; q < nb; ++q) {
+            if (y >= S.boxes[q][1] && y < S.boxes[q][3]) {
+                const int lo = max((int)S.boxes[q][0], 32 * w) - 32 * w;
+                const int hi = min((int)S.boxes[q][2], 32 * w + 32) - 32 * w;
+                if (hi > lo) {
+                    const uint32_t m = ((hi >= 32) ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+                    c1 |= c0 & m;
+                    c0 |= m;
+                }
+            }
+        }
+        S.list[y * (kDst / 32) + w] = c0;
+        S.list[kPlaneWords + y * (kDst / 32) + w] = c1;
+    }
+}
+// the 4 GT weights of quad cq in row y from the planes: 0 / 1 (VGG-SS) or 0 / 1 / 2 (Flickr)
+__device__ __forceinline__ uint32_t planes_quad(const EvalSmem& S, int gt_mode, int cq, int y) {
+    const int i = y * (kDst / 32) + (cq >> 3), sh = 4 * (cq & 7);
+    uint32_t g4 = (((S.list[i] >> sh) & 15u) * 0x00204081u) & 0x01010101u;
+    if (gt_mode == AVT_GT_FLICKR) g4 += (((S.list[kPlaneWords + i] >> sh) & 15u) * 0x00204081u) & 0x01010101u;
+    return g4;
+}
+
 __device__ __forceinline__ uint32_t boxes_quad(const EvalSmem& S, int nb, int gt_mode, int x0, int y) {
     uint32_t g4 = 0;
 #pragma unroll
@@ -408,7 +441,9 @@ __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int n
                                 (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
             if (kMask) AVT_ST(reinterpret_cast<unsigned int*>(mk_p + r * kDst), m4);
             const uint32_t gr = (r == 0) ? g.x : (r == 1) ? g.y : (r == 2) ? g.z : g.w;
-            const uint32_t g4 = kDenseGt ? gr : boxes_quad(S, nb, gt_mode, 4 * cq, t.y0 + h + r);
+            const uint32_t g4 = kDenseGt ? gr
+                              : (gt_mode == AVT_GT_FLICKR_FRAME ? boxes_quad(S, nb, gt_mode, 4 * cq, t.y0 + h + r)
+                                                                : planes_quad(S, gt_mode, cq, t.y0 + h + r));
             inter = __dp4a(m4, g4, inter);
             gsum = __dp4a(g4, 0x01010101u, gsum);
             zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
@@ -684,6 +719,11 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
             const uint3 c3 = final_sweep_keys<kDenseGt>(S, k_on, nb, gt_mode, up_o, mk_o, gt_i);
             inter = c3.x; gsum = c3.y; zc = c3.z;
         } else {
+            if (!kDenseGt && gt_mode != AVT_GT_FLICKR_FRAME) {       // the selection is over: reuse its list
+                __syncthreads();
+                rasterise_planes(S, nb);
+                __syncthreads();
+            }
             if (up_o) { if (mk_o) AVT_FINAL(true, true); else AVT_FINAL(true, false); }
             else { if (mk_o) AVT_FINAL(false, true); else AVT_FINAL(false, false); }
         }

@@ -419,6 +419,16 @@ def extras(avt, ev, _lib, cfg, dev, pk):
                                      "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"], "traffic": None}}
     ms2 = timed(lambda: run_eval(False), 10, 3)
     out["eval_cfg3_metrics_only"] = {"maps_per_s": n / (ms2 * 1e-3), "ms": ms2}
+    # the pipeline mode of the reference's test loop: boxes in (utils.py:264-273 rasterised inside
+    # the kernel as bit planes), scalars out -- nothing but 784 B + a few boxes read per clip
+    bxs = torch.tensor([[[50, 40, 180, 160], [10, 100, 90, 200]]], dtype=torch.int16, device=dev).repeat(n, 1, 1).contiguous()
+    bcs = torch.full((n,), 2, dtype=torch.uint8, device=dev)
+
+    def run_eval_boxes():
+        _lib.check(lib.avt_eval_maps(_lib.ptr(maps), n, None, _lib.ptr(bxs), _lib.ptr(bcs), 2, 0, None, None,
+                                     _lib.ptr(iw), _lib.ptr(uw), _lib.ptr(ci), _lib.stream_ptr()), "avt_eval_maps")
+    ms3 = timed(run_eval_boxes, 10, 3)
+    out["eval_cfg3_boxes_in_scalars_out"] = {"maps_per_s": n / (ms3 * 1e-3), "ms": ms3}
     # the reference's CPU eval glue (restated, cv2-free) on a bounded sample, single core
     t0 = time.perf_counter()
     ns = 200
