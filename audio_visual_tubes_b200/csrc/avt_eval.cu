@@ -404,7 +404,22 @@ __device__ __forceinline__ uint32_t boxes_quad(const EvalSmem& S, int nb, int gt
 // Final sweep: materialise, binarise, read / rasterise the GT, count.  Straight-line per strip:
 // the 8 GT words of a strip are requested before any arithmetic, the up-sampled row is computed
 // once and feeds the store, the compare and the counts.
-template <bool kDenseGt, bool kUp, bool kMask>
+// {u >= t} of four floats as 0 / 1 bytes: four SETs (all-ones / zero), three byte permutes, one AND
+__device__ __forceinline__ uint32_t ge_mask4(const float4& u, float t) {
+    uint32_t m0, m1, m2, m3, p, q, r;
+    asm("set.ge.u32.f32 %0, %1, %2;" : "=r"(m0) : "f"(u.x), "f"(t));
+    asm("set.ge.u32.f32 %0, %1, %2;" : "=r"(m1) : "f"(u.y), "f"(t));
+    asm("set.ge.u32.f32 %0, %1, %2;" : "=r"(m2) : "f"(u.z), "f"(t));
+    asm("set.ge.u32.f32 %0, %1, %2;" : "=r"(m3) : "f"(u.w), "f"(t));
+    asm("prmt.b32 %0, %1, %2, 0x0040;" : "=r"(p) : "r"(m0), "r"(m1));
+    asm("prmt.b32 %0, %1, %2, 0x0040;" : "=r"(q) : "r"(m2), "r"(m3));
+    asm("prmt.b32 %0, %1, %2, 0x5410;" : "=r"(r) : "r"(p), "r"(q));
+    return r & 0x01010101u;
+}
+
+// kSmallGt: GT weights are at most 2 (VGG-SS union, Flickr clipped count), so "weight == 0" is
+// three integer ops per quad instead of a byte-wise compare.
+template <bool kDenseGt, bool kUp, bool kMask, bool kSmallGt>
 __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int nb, int gt_mode,
                                             float* __restrict__ up_o, uint8_t* __restrict__ mk_o,
                                             const uint8_t* __restrict__ gt_i,
@@ -437,8 +452,7 @@ __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int n
             u.z = lerp_rn(t.a.z, w0, t.b.z, w1); u.w = lerp_rn(t.a.w, w0, t.b.w, w1);
             w1 += t.dw;
             if (kUp) AVT_ST(reinterpret_cast<float4*>(up_p + r * kDst), u);
-            const uint32_t m4 = (u.x >= t_on ? 1u : 0u) | (u.y >= t_on ? 0x100u : 0u) |
-                                (u.z >= t_on ? 0x10000u : 0u) | (u.w >= t_on ? 0x1000000u : 0u);
+            const uint32_t m4 = ge_mask4(u, t_on);
             if (kMask) AVT_ST(reinterpret_cast<unsigned int*>(mk_p + r * kDst), m4);
             const uint32_t gr = (r == 0) ? g.x : (r == 1) ? g.y : (r == 2) ? g.z : g.w;
             const uint32_t g4 = kDenseGt ? gr
@@ -446,7 +460,8 @@ __device__ __forceinline__ void final_sweep(const EvalSmem& S, float t_on, int n
                                                                 : planes_quad(S, gt_mode, cq, t.y0 + h + r));
             inter = __dp4a(m4, g4, inter);
             gsum = __dp4a(g4, 0x01010101u, gsum);
-            zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
+            if (kSmallGt) zc = __dp4a(m4, ~((g4 + 0x7f7f7f7fu) >> 7) & 0x01010101u, zc);
+            else zc = __dp4a(m4, __vcmpeq4(g4, 0u) & 0x01010101u, zc);
         }
         if (kDenseGt) g = gn;
     }
@@ -714,7 +729,13 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
         float* up_o = up224 ? up224 + (size_t)map * kNpix : nullptr;
         uint8_t* mk_o = mask ? mask + (size_t)map * kNpix : nullptr;
         const uint8_t* gt_i = kDenseGt ? gt_dense + (size_t)map * kNpix : nullptr;
-#define AVT_FINAL(UP, MK) final_sweep<kDenseGt, UP, MK>(S, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc)
+#define AVT_FINAL(UP, MK)                                                                                  \
+    do {                                                                                                   \
+        if (gt_mode != AVT_GT_FLICKR_FRAME)                                                                \
+            final_sweep<kDenseGt, UP, MK, true>(S, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc);  \
+        else                                                                                               \
+            final_sweep<kDenseGt, UP, MK, false>(S, t_on, nb, gt_mode, up_o, mk_o, gt_i, inter, gsum, zc); \
+    } while (0)
         if (key_cmp) {
             const uint3 c3 = final_sweep_keys<kDenseGt>(S, k_on, nb, gt_mode, up_o, mk_o, gt_i);
             inter = c3.x; gsum = c3.y; zc = c3.z;
