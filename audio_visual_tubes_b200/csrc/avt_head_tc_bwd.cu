@@ -13,6 +13,7 @@
 //
 // All three are TMA-fed tcgen05 kernels with the accumulators in tensor memory.
 #include "avt_common.cuh"
+#include <mutex>
 #include "avt_tc.cuh"
 #include <stdlib.h>
 
@@ -638,6 +639,34 @@ int launch_grad_cells_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, c
                            const float* sim, const float* den, const float* gsim, const float* GA,
                            __nv_bfloat16* G, cudaStream_t st);
 
+// The dv and d_ahat contractions both consume G and are independent of each other: d_ahat is
+// enqueued on a side stream so that its CTAs fill the SMs the dv kernel's last wave leaves idle
+// (matters for small shards: at 128 rows per rank the two kernels are ~1.3 waves each).  Plain
+// event fork / join, so it is captured into CUDA graphs like any cross-stream dependency.
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr, fork0 = nullptr, tdone = nullptr;
+};
+static SideStream* side_stream(int dev) {
+    static std::mutex mu;
+    static SideStream ctx[64];
+    if (dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    SideStream& c = ctx[dev];
+    if (!c.stream) {
+        if (cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c.join, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c.fork0, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c.tdone, cudaEventDisableTiming) != cudaSuccess) {
+            c.stream = nullptr;
+            (void)cudaGetLastError();
+            return nullptr;
+        }
+    }
+    return &c;
+}
+
 int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
                     __nv_bfloat16* at_bf, __nv_bfloat16* g_bf, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C, int P,
@@ -650,14 +679,28 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
     AVT_CHECK_CUDA(cudaGetDevice(&dev));
     AVT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 
+    // the side stream first transposes the audio operand of stage 2 while stage 1 runs, then (after
+    // stage 1) carries stage 3 concurrently with stage 2
+    SideStream* side = getenv("AVT_NO_SIDE_STREAM") ? nullptr : side_stream(dev);
+    cudaStream_t st_da = side ? side->stream : st;
+    if (side) {
+        AVT_CHECK_CUDA(cudaEventRecord(side->fork0, st));
+        AVT_CHECK_CUDA(cudaStreamWaitEvent(side->stream, side->fork0, 0));
+    }
+    {
+        dim3 grid(n_a_pad / 32, C / 32), block(32, 8);
+        transpose_audio_kernel<<<grid, block, 0, st_da>>>(a_bf, n_a_pad, C, at_bf);
+        AVT_LAUNCH_CHECK();
+    }
+    if (side) AVT_CHECK_CUDA(cudaEventRecord(side->tdone, side->stream));
     // stage 1: cell gradients
     int rc = launch_grad_cells_bf16(vt, a_bf, pos_idx, col_offset, N_v, N_a, n_a_pad, C, P, hp, sim, den,
                                     gsim, GA, g_bf, st);
     if (rc != AVT_OK) return rc;
-    {
-        dim3 grid(n_a_pad / 32, C / 32), block(32, 8);
-        transpose_audio_kernel<<<grid, block, 0, st>>>(a_bf, n_a_pad, C, at_bf);
-        AVT_LAUNCH_CHECK();
+    if (side) {
+        AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->tdone, 0));
+        AVT_CHECK_CUDA(cudaEventRecord(side->fork, st));
+        AVT_CHECK_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
     }
     // stage 2: dv
     {
@@ -688,7 +731,7 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
     }
     // stage 3: d_ahat (zeroed by the caller)
     {
-        ProfScope _ps(kProfBwdDa, st);
+        ProfScope _ps(kProfBwdDa, st_da);
         const int n_mt = n_a_pad / kDaBM;
         const bool pair = (n_mt % 2 == 0) && (C == 256 || C == 512) && !getenv("AVT_NO_PAIR");
         const int bk = pair ? kDa2BK : kDaBK;
@@ -712,15 +755,19 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
         if (pair) {
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDa2SmemBytes));
-            bwd_da_pair_kernel<<<n_mt * splits, kDa2Threads, kDa2SmemBytes, st>>>(map_g, map_vt, d_ahat, N_a,
+            bwd_da_pair_kernel<<<n_mt * splits, kDa2Threads, kDa2SmemBytes, st_da>>>(map_g, map_vt, d_ahat, N_a,
                                                                                   n_mt, splits, n_chunks, C);
         } else {
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDaSmemBytes));
-            bwd_da_kernel<<<n_mt * splits, kDaThreads, kDaSmemBytes, st>>>(map_g, map_vt, d_ahat, N_a, n_mt,
+            bwd_da_kernel<<<n_mt * splits, kDaThreads, kDaSmemBytes, st_da>>>(map_g, map_vt, d_ahat, N_a, n_mt,
                                                                           splits, n_chunks, C);
         }
         AVT_LAUNCH_CHECK();
+    }
+    if (side) {                                      // join
+        AVT_CHECK_CUDA(cudaEventRecord(side->join, side->stream));
+        AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->join, 0));
     }
     return AVT_OK;
 }
