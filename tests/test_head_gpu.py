@@ -268,6 +268,33 @@ def test_graph_captured_step_equals_eager():
         assert relnorm(da1.cpu().numpy(), da0.cpu().numpy()) < 1e-5
 
 
+def test_host_pipeline_tracks_each_steps_inputs():
+    """HostHeadPipeline overlaps the H2D of step i+1 with the compute of step i on two slots:
+    every handle must report the loss and gradients of ITS OWN host inputs, in any read order."""
+    from audio_visual_tubes_b200 import HeadConfig, HostHeadPipeline, hardway_value_and_grad
+    cfg = HeadConfig()
+    feats = [head_features(24, 24, s, "mix") for s in (91, 92, 93, 94, 95)]
+    host = [(torch.tensor(v).pin_memory(), torch.tensor(a).pin_memory()) for v, a in feats]
+    want = []
+    for v, a in feats:
+        l, dv, da = hardway_value_and_grad(torch.tensor(v, device="cuda"), torch.tensor(a, device="cuda"), cfg)
+        want.append((float(l.cpu()[0]), dv.cpu(), da.cpu()))
+    pipe = HostHeadPipeline(feats[0][0].shape, feats[0][1].shape, cfg)
+    pend, got = None, []
+    for vh, ah in host:
+        h = pipe.submit(vh, ah)
+        if pend is not None:
+            dv, da = pend.grads()
+            got.append((pend.loss(), dv.cpu(), da.cpu()))
+        pend = h
+    dv, da = pend.grads()
+    got.append((pend.loss(), dv.cpu(), da.cpu()))
+    assert len({w[0] for w in want}) == len(want)           # the five steps really differ
+    for (l0, dv0, da0), (l1, dv1, da1) in zip(want, got):
+        assert l0 == l1 and torch.equal(dv0, dv1)
+        assert relnorm(da1.numpy(), da0.numpy()) < 1e-5
+
+
 def test_errors_are_loud():
     from audio_visual_tubes_b200 import HeadConfig, hardway_head
     v, a = head_features(2, 2, 1, "relu")
