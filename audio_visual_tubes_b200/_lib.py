@@ -34,7 +34,7 @@ SIGNATURES = {
     "avt_head_forward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
                               _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
     "avt_head_backward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
-                               _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _z, _p]),
+                               _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _z, _p]),
     "avt_eval_maps": (_i, [_p, _i, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p]),
     "avt_eval_stats": (_i, [_p, _i]),
     "avt_ciou_counts": (_i, [_p, _f, _p, _i, _i, _p, _p, _p, _p]),

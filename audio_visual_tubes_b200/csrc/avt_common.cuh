@@ -129,6 +129,12 @@ int launch_bwd_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, const float* gsim,
                     const float* GA, float* dvh, float* dah, cudaStream_t st);
+// backward of weighted_A (avt_head_weighted.cu)
+int launch_weighted_row_grad(const float* A, const float* msum, const float* gW, const float* dA_in,
+                             int N_v, int P, int C, HeadParams hp, float* dA_out, float* u_out,
+                             cudaStream_t st);
+int launch_weighted_dv(const float* v, const float* rnorm_v, const float* msum, const float* u,
+                       int N_v, int C, int P, float* dv, cudaStream_t st);
 int launch_dv_finish(const float* v, const float* rnorm_v, int N_v, int C, int P, float* dv,
                      cudaStream_t st);
 // tcgen05 path (avt_head_tc.cu): vt = normalised maps, bf16 [N_v*P (+slack)][C]; a_bf = audio

@@ -9,7 +9,7 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 // Workspace layout (all offsets 1024-byte aligned).  The forward leaves the bf16 operand
 // copies in place; a backward called with the same workspace reuses them.
 struct HeadWorkspace {
-    size_t scratch, msum, gsim, ga, vt, a_bf, at_bf, g_bf, total;
+    size_t scratch, msum, gsim, ga, da_w, u_w, vt, a_bf, at_bf, g_bf, total;
 };
 
 HeadWorkspace head_workspace_layout(int N_v, int N_a, int C, int P, int precision, int backward) {
@@ -18,7 +18,7 @@ HeadWorkspace head_workspace_layout(int N_v, int N_a, int C, int P, int precisio
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 1024); return o; };
     w.scratch = take(sizeof(HeadScratch));
     w.msum = take((size_t)N_v * P * sizeof(float));
-    w.gsim = w.ga = w.vt = w.a_bf = w.at_bf = w.g_bf = 0;
+    w.gsim = w.ga = w.da_w = w.u_w = w.vt = w.a_bf = w.at_bf = w.g_bf = 0;
     if (precision == AVT_PRECISION_BF16) {
         const size_t n_a_pad = (size_t)n_a_padded(N_a);
         // + one tile of slack rows so the last image's 208-row TMA box stays in bounds
@@ -32,6 +32,8 @@ HeadWorkspace head_workspace_layout(int N_v, int N_a, int C, int P, int precisio
     if (backward) {
         w.gsim = take((size_t)N_v * N_a * sizeof(float));
         w.ga = take((size_t)N_v * P * sizeof(float));
+        w.da_w = take((size_t)N_v * P * sizeof(float));      // weighted_A backward: dA total, u
+        w.u_w = take((size_t)N_v * P * sizeof(float));
     }
     w.total = off;
     return w;
@@ -121,7 +123,8 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
                                  int precision, int col_mult, const float* A, const float* logits,
                                  const float* loss_rows, const float* rnorm_v, const float* sim,
                                  const float* den, float dloss_scale, const float* dlogits,
-                                 const float* dA, float* dv, float* d_ahat, void* workspace,
+                                 const float* dA, const float* dWeighted, float* dv,
+                                 float* d_ahat, void* workspace,
                                  size_t workspace_bytes, void* stream) {
     int rc = check_shapes("avt_head_backward", N_v, N_a, C, P, precision);
     if (rc != AVT_OK) return rc;
@@ -141,6 +144,14 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
     float* gsim = reinterpret_cast<float*>(ws + w.gsim);
     float* GA = reinterpret_cast<float*>(ws + w.ga);
 
+    const float* msum = reinterpret_cast<const float*>(ws + w.msum);   // left by the forward
+    float* u_w = reinterpret_cast<float*>(ws + w.u_w);
+    if (dWeighted) {            // model.py:148-152: fold the map part into dA, keep u for dv
+        float* da_w = reinterpret_cast<float*>(ws + w.da_w);
+        rc = launch_weighted_row_grad(A, msum, dWeighted, dA, N_v, P, C, hp, da_w, u_w, st);
+        if (rc != AVT_OK) return rc;
+        dA = da_w;
+    }
     rc = launch_row_grad(A, logits, loss_rows, pos_idx, col_offset, N_v, N_a, P, hp, dloss_scale,
                          dlogits, dA, gsim, GA, sim, col_mult, st);
     if (rc != AVT_OK) return rc;
@@ -150,7 +161,9 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
         rc = launch_bwd_fp32(v, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a, C, P, hp, gsim, GA, dv,
                              d_ahat, st);
         if (rc != AVT_OK) return rc;
-        return launch_dv_finish(v, rnorm_v, N_v, C, P, dv, st);
+        rc = launch_dv_finish(v, rnorm_v, N_v, C, P, dv, st);
+        if (rc != AVT_OK || !dWeighted) return rc;
+        return launch_weighted_dv(v, rnorm_v, msum, u_w, N_v, C, P, dv, st);
     }
     if (!avt_device_ok()) {
         set_error("avt_head_backward: the bf16 tcgen05 path needs an sm_100 device");
@@ -161,6 +174,8 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
     __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
     __nv_bfloat16* at_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.at_bf);
     __nv_bfloat16* g_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.g_bf);
-    return launch_bwd_bf16(v, vt, a_bf, at_bf, g_bf, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
-                           n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, st);
+    rc = launch_bwd_bf16(v, vt, a_bf, at_bf, g_bf, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
+                         n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, st);
+    if (rc != AVT_OK || !dWeighted) return rc;
+    return launch_weighted_dv(v, rnorm_v, msum, u_w, N_v, C, P, dv, st);
 }

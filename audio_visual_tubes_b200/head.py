@@ -100,7 +100,7 @@ def head_forward_raw(v, a_hat, cfg: HeadConfig, pos_idx=None, col_offset=0, want
 
 
 def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits=None, dA=None,
-                      col_offset=0):
+                      col_offset=0, dW=None):
     """One ``avt_head_backward`` call.  Returns (dv [N_v,C,P], d_ahat [N_a,C])."""
     lib = _lib.load()
     n_v, c, p = v.shape
@@ -116,6 +116,8 @@ def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits
         dlogits = dlogits.contiguous().float()
     if dA is not None:
         dA = dA.contiguous().float().view(n_v, p)
+    if dW is not None:
+        dW = dW.contiguous().float().view(n_v, p)
     with torch.cuda.device(v.device):
         rc = lib.avt_head_backward(
             _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(saved["pos_idx"]), int(col_offset),
@@ -123,7 +125,8 @@ def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits
             prec, int(saved.get("col_mult", 1)), _lib.ptr(saved["A"]), _lib.ptr(saved["logits"]),
             _lib.ptr(saved["loss_rows"]),
             _lib.ptr(saved["rnorm_v"]), _lib.ptr(saved["sim"]), _lib.ptr(saved["den"]),
-            float(dloss_scale), _lib.ptr(dlogits), _lib.ptr(dA), _lib.ptr(dv), _lib.ptr(d_ahat),
+            float(dloss_scale), _lib.ptr(dlogits), _lib.ptr(dA), _lib.ptr(dW), _lib.ptr(dv),
+            _lib.ptr(d_ahat),
             _lib.ptr(ws), C.c_size_t(ws.numel()), _lib.stream_ptr())
     _lib.check(rc, "avt_head_backward")
     return dv, d_ahat
@@ -168,14 +171,16 @@ def reduce_tube_dlogits(g_full, out, cfg: HeadConfig, copy_idx):
 class _HardWayHead(torch.autograd.Function):
     """autograd wrapper: (v, a) -> (A, logits, Pos, Neg, weighted_A, loss_rows).
 
-    Gradients flow through ``logits``, ``A`` and ``loss_rows`` (the fused
-    CrossEntropyLoss(target 0) per row).  ``Pos`` / ``Neg`` / ``weighted_A`` are returned
-    for inspection exactly like the reference returns them and are non-differentiable here
-    (no reference training script back-propagates through them)."""
+    Gradients flow through ``logits``, ``A``, ``weighted_A`` (train_hardway.py:138-142 sends an
+    MSE and the PropagationLoss back through it) and ``loss_rows`` (the fused
+    CrossEntropyLoss(target 0) per row).  ``Pos`` / ``Neg`` are returned for inspection exactly
+    like the reference returns them and are non-differentiable here (no reference training
+    script back-propagates through them)."""
 
     @staticmethod
     def forward(ctx, v, a, cfg, pos_idx, col_offset, want_weighted, col_mult=1, copy_idx=None):
         need_grad = v.requires_grad or a.requires_grad
+        ctx.set_materialize_grads(False)      # unused outputs arrive as None, not as zero tensors
         v = v.contiguous().float()
         a_hat, rn_a = audio_normalize(a)
         out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, want_weighted, for_backward=need_grad,
@@ -185,7 +190,11 @@ class _HardWayHead(torch.autograd.Function):
         ctx.copy_idx = copy_idx
         ctx.save_for_backward(v, a_hat, rn_a)
         w = out["weighted_A"] if want_weighted else out["A"].new_empty(0)
-        ctx.mark_non_differentiable(out["Pos"], out["Neg"], w)
+        ctx.want_weighted = want_weighted
+        if want_weighted:
+            ctx.mark_non_differentiable(out["Pos"], out["Neg"])
+        else:
+            ctx.mark_non_differentiable(out["Pos"], out["Neg"], w)
         logits = out["logits"] if col_mult == 1 else expand_tube_logits(out, cfg, copy_idx)
         ctx.logits_full = logits
         return out["A"], logits, out["Pos"], out["Neg"], w, out["loss_rows"]
@@ -207,7 +216,7 @@ class _HardWayHead(torch.autograd.Function):
         if dlogits is not None and ctx.saved["col_mult"] > 1:
             dlogits = reduce_tube_dlogits(dlogits.contiguous().float(), ctx.saved, ctx.cfg, ctx.copy_idx)
         dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, scale, dlogits, gA,
-                                       ctx.col_offset)
+                                       ctx.col_offset, gW if ctx.want_weighted else None)
         da = audio_normalize_backward(a_hat, rn_a, d_ahat)
         return dv, da, None, None, None, None, None, None
 

@@ -121,7 +121,11 @@ int avt_head_forward(const float* v, const float* a_hat,
 
 /* Backward of the head (autograd of model.py:117-146 + CrossEntropyLoss).
  * Gradient of   dloss_scale * sum_n loss_rows[n]  +  <dlogits, logits>  +  <dA, A>
- * (dlogits, dA may be NULL).  Writes dv [N_v, C, P] (gradient wrt the RAW maps) and
+ *               +  <dWeighted, weighted_A>
+ * (dlogits, dA, dWeighted [N_v, P] may be NULL; dWeighted is what train_hardway.py:138-142
+ * sends back through weighted_A = mean_c(v_hat * normalize(Pos)), model.py:148-152: it
+ * reaches v through every channel alike and through Pos -> A; needs the workspace the forward
+ * ran with, which still holds mean_c v_hat).  Writes dv [N_v, C, P] (gradient wrt the RAW maps) and
  * d_ahat [N_a, C] (gradient wrt the NORMALISED audio rows, summed over this call's
  * N_v rows; finish with avt_audio_normalize_backward, after a reduce-scatter when
  * rows are sharded over ranks). */
@@ -133,6 +137,7 @@ int avt_head_backward(const float* v, const float* a_hat,
                       const float* A, const float* logits, const float* loss_rows,
                       const float* rnorm_v, const float* sim, const float* den,
                       float dloss_scale, const float* dlogits, const float* dA,
+                      const float* dWeighted,
                       float* dv, float* d_ahat,
                       void* workspace, size_t workspace_bytes, void* stream);
 

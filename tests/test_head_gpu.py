@@ -295,6 +295,67 @@ def test_host_pipeline_tracks_each_steps_inputs():
         assert relnorm(da1.numpy(), da0.numpy()) < 1e-5
 
 
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("n,mode", [(12, "mix"), (8, "relu"), (5, "signed")])
+def test_weighted_map_gradient_vs_oracle(n, mode, precision):
+    """avt_head_backward's dWeighted (model.py:148-152 back-propagated as train_hardway.py:138-142
+    does): <dW, weighted_A> alone, and together with the loss, dlogits and dA."""
+    from audio_visual_tubes_b200 import HeadConfig, hardway_head
+    v, a = head_features(n, n, 70 + n, mode)
+    rng = np.random.default_rng(n)
+    dW = rng.standard_normal((n, 196)).astype(np.float32)
+    dA = (0.01 * rng.standard_normal((n, 196))).astype(np.float32)
+    cfg = HeadConfig(precision=precision)
+    for scale, use_dA in ((0.0, False), (1.0, True)):
+        o, dv, da = ho.head_forward_backward_torch(v, a, loss_scale=scale, dW=dW, dA=dA if use_dA else None)
+        vt = torch.tensor(v, device="cuda", requires_grad=True)
+        at = torch.tensor(a, device="cuda", requires_grad=True)
+        A, logits, Pos, Neg, wA, loss_rows = hardway_head(vt, at, cfg, return_weighted=True)
+        total = (torch.tensor(dW, device="cuda") * wA).sum()
+        if scale:
+            total = total + scale * loss_rows.mean() + (torch.tensor(dA, device="cuda") * A).sum()
+        total.backward()
+        assert rel(wA.detach().cpu().numpy(), o["weighted_A"]) < TOL[precision][0]
+        # the channel-uniform part of dv is exact fp32 in both precisions; the part through
+        # Pos -> A rides the bf16 contraction like every other map gradient
+        assert relnorm(vt.grad.cpu().numpy(), dv) < TOL[precision][1], (scale, relnorm(vt.grad.cpu().numpy(), dv))
+        assert relnorm(at.grad.cpu().numpy(), da) < TOL[precision][1], (scale, relnorm(at.grad.cpu().numpy(), da))
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_hardway16_objective_matches_reference_golden(precision):
+    """The 16-frame training objective (train_hardway.py:132-142) through the product: two head
+    passes with return_weighted, the losses.py mirror, one backward -- against the UNMODIFIED
+    reference's values and gradients (tests/golden/make_golden_aux.py)."""
+    from audio_visual_tubes_b200 import HeadConfig, hardway_head, hardway16_objective
+    G = np.load(os.path.join(GOLD, "head_aux_golden.npz"))
+    b, t, seed = (int(x) for x in G["meta"])
+    lw = float(G["loss_weight"])
+    n = b * t
+    v1, a = head_features(n, b, seed, "mix")
+    v2, _ = head_features(n, b, seed + 1, "mix")
+    cfg = HeadConfig(precision=precision)
+    f1 = torch.tensor(v1, device="cuda", requires_grad=True)
+    f2 = torch.tensor(v2, device="cuda", requires_grad=True)
+    spec = torch.tensor(a, device="cuda", requires_grad=True)
+    spec_rep = spec.repeat_interleave(t, dim=0)                  # train_hardway.py:128-129
+    out1 = hardway_head(f1, spec_rep, cfg, return_weighted=True)
+    out2 = hardway_head(f2, spec_rep, cfg, return_weighted=True)
+    combined, hardway, aug, l2, cons = hardway16_objective(out1, out2, b, t, lw)
+    combined.backward()
+    tol_f, tol_g = TOL[precision]
+    assert rel(out1[4].detach().cpu().numpy(), G["weighted"]) < max(tol_f, 2e-5)
+    assert abs(float(hardway) - G["hardway"]) < tol_f and abs(float(aug) - G["aug"]) < tol_f
+    assert abs(float(cons) - G["consistency"]) < tol_f * G["consistency"] + 1e-7
+    assert abs(float(l2) - G["l2"]) < 2 * tol_f * G["l2"] + 1e-8
+    assert abs(float(combined) - G["combined"]) < tol_f
+    dv1 = f1.grad.cpu().numpy()
+    assert relnorm(dv1[:, ::16, ::2], G["dv1_sub"]) < tol_g
+    assert relnorm(f2.grad.cpu().numpy()[:, ::16, ::2], G["dv2_sub"]) < tol_g
+    assert relnorm(np.sqrt((dv1.astype(np.float64) ** 2).sum((1, 2))), G["dv1_norm"]) < tol_g
+    assert relnorm(spec.grad.cpu().numpy(), G["da"]) < tol_g
+
+
 def test_errors_are_loud():
     from audio_visual_tubes_b200 import HeadConfig, hardway_head
     v, a = head_features(2, 2, 1, "relu")

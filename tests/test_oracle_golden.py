@@ -162,3 +162,28 @@ def test_mtc_matches_reference():
     n = int(EVAL["eval/meta"][0])
     gmask = np.unpackbits(EVAL["eval/mask_packed"])[: n * 224 * 224].reshape(n, 224, 224)
     assert abs(eo.mtc(list(gmask[16:24])) - float(EVAL["eval/mtc_16_24"])) < 1e-6
+
+
+def test_hardway16_objective_matches_reference():
+    """train_hardway.py:132-142 (two AVENet passes, CE + MSE(weighted) + PropagationLoss) from the
+    UNMODIFIED reference (tests/golden/make_golden_aux.py) pins the oracle's weighted_A and its
+    gradient: one oracle pass per frame set, the other set's weighted map held constant."""
+    G = np.load(os.path.join(GOLD, "head_aux_golden.npz"))
+    b, t, seed = (int(x) for x in G["meta"])
+    lw = float(G["loss_weight"])
+    n = b * t
+    v1, a = head_features(n, b, seed, "mix")
+    v2, _ = head_features(n, b, seed + 1, "mix")
+    a_rep = np.repeat(a, t, axis=0)                              # train_hardway.py:128-129
+    o1, dv1, da1 = ho.head_forward_backward_torch(v1, a_rep, loss_scale=lw / 2,
+                                                  aux=(b, t, 1.0, 100 - lw, G["weighted2"]))
+    o2, dv2, da2 = ho.head_forward_backward_torch(v2, a_rep, loss_scale=lw / 2,
+                                                  aux=(b, t, 1.0, 100 - lw, G["weighted"]))
+    assert rel(o1["weighted_A"], G["weighted"]) < 2e-5 and rel(o2["weighted_A"], G["weighted2"]) < 2e-5
+    assert abs(o1["loss"] * lw - G["hardway"]) < 1e-5 and abs(o2["loss"] * lw - G["aug"]) < 1e-5
+    assert abs(o1["consistency"] + o2["consistency"] - G["consistency"]) < 1e-6 * max(1, G["consistency"])
+    assert abs(o1["l2"] * (100 - lw) - G["l2"]) < 2e-4 * G["l2"]
+    assert rel(dv1[:, ::16, ::2], G["dv1_sub"]) < 5e-4 and rel(dv2[:, ::16, ::2], G["dv2_sub"]) < 5e-4
+    assert rel(np.sqrt((dv1 ** 2).sum((1, 2))), G["dv1_norm"]) < 5e-4
+    da = (da1 + da2).reshape(b, t, -1).sum(1)
+    assert rel(da, G["da"]) < 5e-4
