@@ -41,6 +41,7 @@ SIGNATURES = {
     "avt_rasterise_gt": (_i, [_p, _p, _i, _i, _i, _p, _p]),
     "avt_auc": (_i, [_p, _i, _p, _p, _p]),
     "avt_mtc": (_i, [_p, _i, _p, _p, _p, _p]),
+    "avt_video_metrics": (_i, [_p, _p, _i, _i, _p, _p, _p, _p]),
 }
 
 _lib = None

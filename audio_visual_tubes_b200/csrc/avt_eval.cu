@@ -861,6 +861,45 @@ __global__ void mtc_mean_kernel(const int32_t* __restrict__ pair_inter,
     }
 }
 
+// train_hardway.py:163-203, the per-video metrics of the PerFrameLabels test loop: video v owns
+// frames [v*F, (v+1)*F).  out[v] = { #(ciou >= 0.5)/F  (:200),  trapezoid AUC of its 21-point
+// success curve (:193-199),  mTC over its F-1 consecutive mask pairs (utils.py:311-318, float32
+// accumulation as the reference's torch tensor; NaN for F == 1 as torch.div(0, 0)) }.
+__global__ void video_metrics_kernel(const double* __restrict__ ciou, const int32_t* __restrict__ pair_inter,
+                                     const int32_t* __restrict__ pair_union, int F,
+                                     double* __restrict__ out) {
+    const int v = blockIdx.x, lane = threadIdx.x;
+    int loc[21];
+#pragma unroll
+    for (int i = 0; i < 21; ++i) loc[i] = 0;
+    int half = 0;
+    for (int j = lane; j < F; j += 32) {
+        const double c = ciou[(size_t)v * F + j];
+#pragma unroll
+        for (int i = 0; i < 21; ++i) loc[i] += (c >= 0.05 * (double)i);
+        half += (c >= 0.5);
+    }
+#pragma unroll
+    for (int i = 0; i < 21; ++i) loc[i] = __reduce_add_sync(0xffffffffu, loc[i]);
+    half = __reduce_add_sync(0xffffffffu, half);
+    if (lane == 0) {
+        double auc = 0.0;
+#pragma unroll
+        for (int i = 0; i < 20; ++i) {
+            const double dx = 0.05 * (double)(i + 1) - 0.05 * (double)i;
+            auc += dx * ((double)loc[i + 1] / (double)F + (double)loc[i] / (double)F) / 2.0;
+        }
+        float acc = 0.f;
+        for (int i = 0; i < F - 1; ++i) {
+            const size_t k = (size_t)v * F + i;
+            acc += (float)((double)pair_inter[k] / (double)pair_union[k]);
+        }
+        out[3 * v + 0] = (double)half / (double)F;
+        out[3 * v + 1] = auc;
+        out[3 * v + 2] = (double)(acc / (float)(F - 1));
+    }
+}
+
 // Evaluator.cal_CIOU (utils.py:209-214) on ready-made maps: infer = (pred >= thres)
 __global__ void ciou_counts_kernel(const float* __restrict__ infer, float thres,
                                    const uint8_t* __restrict__ gt_w, int gt_den,
@@ -978,6 +1017,21 @@ extern "C" int avt_mtc(const uint8_t* masks, int T, int32_t* pair_inter, int32_t
     mtc_pairs_kernel<<<T - 1, 256, 0, st>>>(masks, pair_inter, pair_union);
     AVT_LAUNCH_CHECK();
     mtc_mean_kernel<<<1, 32, 0, st>>>(pair_inter, pair_union, T, out);
+    AVT_LAUNCH_CHECK();
+    return AVT_OK;
+}
+
+extern "C" int avt_video_metrics(const double* ciou, const uint8_t* masks, int V, int F,
+                                 int32_t* pair_inter, int32_t* pair_union, double* out, void* stream) {
+    AVT_REQUIRE(V >= 0 && F >= 1, "avt_video_metrics: V=%d F=%d", V, F);
+    if (V == 0) return AVT_OK;
+    AVT_REQUIRE(ciou && masks && pair_inter && pair_union && out, "avt_video_metrics: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if ((size_t)V * F >= 2) {      // every consecutive pair; the V-1 pairs across videos are not read
+        mtc_pairs_kernel<<<V * F - 1, 256, 0, st>>>(masks, pair_inter, pair_union);
+        AVT_LAUNCH_CHECK();
+    }
+    video_metrics_kernel<<<V, 32, 0, st>>>(ciou, pair_inter, pair_union, F, out);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }

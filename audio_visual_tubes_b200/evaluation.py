@@ -200,6 +200,45 @@ def evaluate_maps(maps14, boxes=None, gt_dense=None, gt_mode="vggss", want_up224
     return r
 
 
+def evaluate_videos(maps14, boxes=None, gt_dense=None, gt_mode="flickr_frame", device=None):
+    """The PerFrameLabels test loop of the 16-frame model (train_hardway.py:158-203) for V videos
+    of F sampled frames each, without the reference's per-frame ``.cpu().numpy()``.
+
+    maps14: [V,F,14,14] localisation maps (``heatmap[0,0]`` of every sampled frame); ``boxes``:
+    V lists of F per-frame box lists (``testset_gt_frame`` units, utils.py:276-309) or ``gt_dense``
+    [V,F,224,224] uint8 weights.  Returns dict(ciou [V,F] float64, per_video [V,3] float64 =
+    (cIoU@0.5 fraction, AUC, mTC) per video, ciou_mean, auc_mean, mtc_mean = the three numbers the
+    reference prints (:201-203)); device tensors except the three means (one D2H of V*3 doubles)."""
+    dev = _dev(device if device is not None else (maps14.device if isinstance(maps14, torch.Tensor) and maps14.is_cuda else None))
+    m = _to_dev(maps14, torch.float32, dev)
+    if m.dim() != 4 or m.shape[2:] != (14, 14):
+        raise ValueError(f"evaluate_videos: maps14 must be [V,F,14,14], got {tuple(m.shape)}")
+    nv, nf = int(m.shape[0]), int(m.shape[1])
+    bx = bc = None
+    if gt_dense is not None:
+        gt_dense = _to_dev(gt_dense, torch.uint8, dev).reshape(nv * nf, 224, 224)
+    else:
+        if len(boxes) != nv or any(len(b) != nf for b in boxes):
+            raise ValueError("evaluate_videos: boxes must be V lists of F per-frame box lists")
+        bx, bc = pack_boxes([fb for vb in boxes for fb in vb], gt_mode)
+        bx, bc = bx.to(dev), bc.to(dev)
+    r = eval_maps_raw(m.reshape(nv * nf, 14, 14), gt_dense, bx, bc, gt_mode, False, True)
+    lib = _lib.load()
+    pi = torch.empty(max(nv * nf - 1, 1), dtype=torch.int32, device=dev)
+    pu = torch.empty_like(pi)
+    per_video = torch.empty(nv, 3, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.avt_video_metrics(_lib.ptr(r["ciou"]), _lib.ptr(r["mask"]), nv, nf, _lib.ptr(pi),
+                                         _lib.ptr(pu), _lib.ptr(per_video), _lib.stream_ptr()),
+                   "avt_video_metrics")
+    pv = per_video.cpu().numpy()
+    return dict(ciou=r["ciou"].view(nv, nf), inter_w=r["inter_w"].view(nv, nf),
+                union_w=r["union_w"].view(nv, nf), mask=r["mask"].view(nv, nf, 224, 224),
+                per_video=per_video,
+                ciou_mean=float(np.sum(pv[:, 0]) / nv), auc_mean=float(np.sum(pv[:, 1]) / nv),
+                mtc_mean=float(np.sum(pv[:, 2]) / nv))
+
+
 def mTC(predictions, gt_maps=None, device=None):
     """utils.py:311-318 -- mean cIoU between consecutive binary predictions (gt_maps unused,
     as in the reference)."""

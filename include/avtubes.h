@@ -190,6 +190,16 @@ int avt_auc(const double* ciou, int N, int32_t* counts, double* out, void* strea
 int avt_mtc(const uint8_t* masks, int T, int32_t* pair_inter, int32_t* pair_union,
             float* out, void* stream);
 
+/* The per-video metrics of the PerFrameLabels test loop, train_hardway.py:163-203: video v owns
+ * frames [v*F, (v+1)*F) of ciou [V*F] float64 and masks [V*F,224,224] uint8 (both as
+ * avt_eval_maps wrote them).  out [V,3] float64 (device):
+ *   out[v][0] = #(ciou >= 0.5) / F                                   train_hardway.py:200
+ *   out[v][1] = sklearn auc of the video's 21-point success curve    :193-199
+ *   out[v][2] = mTC(preds of the video)  utils.py:311-318 (float32 accumulation; NaN if F == 1)
+ * pair_inter, pair_union [V*F-1] int32 scratch (consecutive-mask counts). */
+int avt_video_metrics(const double* ciou, const uint8_t* masks, int V, int F,
+                      int32_t* pair_inter, int32_t* pair_union, double* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

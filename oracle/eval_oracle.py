@@ -218,3 +218,24 @@ def synthetic_maps(n, seed=0):
                                          (yy[None] - cy[:, None, None]) ** 2) /
                                        (2 * sg[:, None, None] ** 2))
     return (base + bump).astype(np.float32)
+
+
+def evaluate_videos(maps14, gts, gt_den=1):
+    """The PerFrameLabels test loop, train_hardway.py:158-203: per video, every sampled frame goes
+    through the single-frame glue (:168-178), then the video's cIoU@0.5 fraction (:200), the AUC
+    of its own 21-point success curve (:193-199) and mTC of its predictions (:185); the dataset
+    numbers are plain means over videos (:201-203).  maps14 [V][F,14,14], gts [V][F] weights."""
+    per_video, cious = [], []
+    for vm, vg in zip(maps14, gts):
+        iou, preds = [], []
+        for m, g in zip(vm, vg):
+            r = evaluate_map(m, g, gt_den)
+            iou.append(r['ciou']); preds.append(r['mask'])
+        iou = np.array(iou, dtype=np.float64)
+        _, results = success_curve(iou)
+        m_tc = mtc(preds) if len(preds) > 1 else float('nan')
+        per_video.append((float(np.sum(iou >= 0.5) / len(iou)), auc_trapezoid(results), m_tc))
+        cious.append(iou)
+    pv = np.array(per_video, dtype=np.float64)
+    return dict(ciou=np.array(cious), per_video=pv, ciou_mean=float(np.sum(pv[:, 0]) / len(pv)),
+                auc_mean=float(np.sum(pv[:, 1]) / len(pv)), mtc_mean=float(np.sum(pv[:, 2]) / len(pv)))

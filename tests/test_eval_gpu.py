@@ -157,3 +157,38 @@ def test_config3_full_size_properties_and_sampled_parity():
     r2 = evaluate_maps(maps[perm], boxes=[boxes[i] for i in perm])
     assert np.array_equal(r2["ciou"].cpu().numpy(), c[perm])
     assert r2["auc"] == r["auc"] and r2["ciou_at_half"] == r["ciou_at_half"]
+
+
+def test_per_video_metrics_match_oracle():
+    """train_hardway.py:158-203 (PerFrameLabels loop): per-video cIoU@0.5 fraction, AUC and mTC,
+    and the three dataset means, against the oracle's restatement of the loop; F == 1 gives the
+    reference's NaN mTC."""
+    from audio_visual_tubes_b200 import evaluate_videos
+    rng = np.random.default_rng(3)
+    nv, nf = 7, 5
+    maps = eo.synthetic_maps(nv * nf, 9).reshape(nv, nf, 14, 14)
+    maps[2, 3] = 0.5                                              # constant frame -> all-zero mask
+    boxes = []
+    for v in range(nv):
+        x0, y0 = rng.integers(0, 120, 2)
+        vb = []
+        for f in range(nf):                                       # a box drifting over the frames
+            bx = [int(x0 + 6 * f), int(y0 + 3 * f), int(x0 + 90 + 6 * f), int(y0 + 110 + 3 * f)]
+            vb.append([bx] if (v + f) % 4 else [bx, [10, 20, 60, 90]])
+        boxes.append(vb)
+    gts = [[eo.rasterise_gt(fb, "flickr_frame")[0] for fb in vb] for vb in boxes]
+    o = eo.evaluate_videos(maps, gts, 1)
+    r = evaluate_videos(maps, boxes=boxes, gt_mode="flickr_frame")
+    assert np.array_equal(r["ciou"].cpu().numpy(), o["ciou"], equal_nan=True)
+    pv = r["per_video"].cpu().numpy()
+    assert np.array_equal(pv[:, 0], o["per_video"][:, 0])
+    assert np.abs(pv[:, 1] - o["per_video"][:, 1]).max() < 1e-12
+    assert np.abs(pv[:, 2] - o["per_video"][:, 2]).max() < 1e-6
+    for k in ("ciou_mean", "auc_mean", "mtc_mean"):
+        assert abs(r[k] - o[k]) < 1e-6, k
+    # dense GT in, same numbers
+    gd = np.array(gts, dtype=np.uint8)
+    r2 = evaluate_videos(torch.tensor(maps, device="cuda"), gt_dense=torch.tensor(gd, device="cuda"))
+    assert torch.equal(r2["per_video"], r["per_video"])
+    r1 = evaluate_videos(maps[:, :1], boxes=[vb[:1] for vb in boxes], gt_mode="flickr_frame")
+    assert np.isnan(r1["per_video"].cpu().numpy()[:, 2]).all() and np.isnan(r1["mtc_mean"])

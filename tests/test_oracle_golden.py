@@ -187,3 +187,17 @@ def test_hardway16_objective_matches_reference():
     assert rel(np.sqrt((dv1 ** 2).sum((1, 2))), G["dv1_norm"]) < 5e-4
     da = (da1 + da2).reshape(b, t, -1).sum(1)
     assert rel(da, G["da"]) < 5e-4
+
+
+def test_per_video_loop_is_the_single_frame_glue_per_video():
+    """oracle evaluate_videos (train_hardway.py:158-203) == evaluate_maps / mtc applied per video."""
+    maps = eo.synthetic_maps(6, 4).reshape(2, 3, 14, 14)
+    gt = [[eo.rasterise_gt([[20 + 10 * f, 30, 150, 200]], "flickr_frame")[0] for f in range(3)] for _ in range(2)]
+    o = eo.evaluate_videos(maps, gt, 1)
+    for v in range(2):
+        e = eo.evaluate_maps(maps[v], gt[v], 1)
+        assert np.array_equal(o["ciou"][v], e["ciou"])
+        assert o["per_video"][v, 0] == e["ciou_at_half"] and o["per_video"][v, 1] == e["auc"]
+        masks = [eo.evaluate_map(m, g, 1)["mask"] for m, g in zip(maps[v], gt[v])]
+        assert o["per_video"][v, 2] == eo.mtc(masks)
+    assert o["auc_mean"] == o["per_video"][:, 1].sum() / 2
