@@ -19,6 +19,8 @@ _p = C.c_void_p
 _i = C.c_int
 _f = C.c_float
 _z = C.c_size_t
+_d = C.c_double
+_ll = C.c_longlong
 
 # name -> (restype, argtypes); mirrors include/avtubes.h line for line
 SIGNATURES = {
@@ -41,6 +43,8 @@ SIGNATURES = {
     "avt_rasterise_gt": (_i, [_p, _p, _i, _i, _i, _p, _p]),
     "avt_auc": (_i, [_p, _i, _p, _p, _p]),
     "avt_mtc": (_i, [_p, _i, _p, _p, _p, _p]),
+    "avt_spectrogram_frames": (_i, [_i]),
+    "avt_log_spectrogram": (_i, [_p, _p, _i, _ll, _i, _p, _d, _d, _d, _p, _i, _p]),
     "avt_video_metrics": (_i, [_p, _p, _i, _i, _p, _p, _p, _p]),
 }
 

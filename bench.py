@@ -506,6 +506,31 @@ def extras(avt, ev, _lib, cfg, dev, pk):
     except Exception as e:
         out["tube_cfg4"] = {"error": repr(e)[:200]}
 
+    # next-4: the dataloader's spectrogram (datasets/dataloader.py:86-96) for a config-2 batch of
+    # 128 ten-second clips at 16 kHz: 4 B read per sample + 4 B written per bin, L2 flushed
+    try:
+        from oracle import spec_oracle as so
+        from audio_visual_tubes_b200.audio import log_spectrogram
+        fs, bs = 16000, 128
+        wav = torch.from_numpy(so.synthetic_waveforms(4, fs, 9)).to(dev).repeat(bs // 4, 1).contiguous()
+        ms = timed(lambda: log_spectrogram(wav, fs), 10, 3, flush)
+        tfr = (fs * 10 - 1) // 511
+        bytes_alg = bs * (fs * 10 * 4 + 257 * tfr * 4)
+        gbs = bytes_alg / (ms * 1e-3) / 1e9
+        t0 = time.perf_counter()
+        w_np = wav[:4].cpu().numpy()
+        reps = 0
+        while time.perf_counter() - t0 < 2.0:
+            so.log_spectrogram(w_np[reps % 4], fs); reps += 1
+        cpu_cps = reps / (time.perf_counter() - t0)
+        out["spectrogram_b128_16k"] = {"clips_per_s": bs / (ms * 1e-3), "ms": ms, "dtype": "f64 arithmetic, f32 out",
+                                       "roofline": {"kernel": "spectrogram_kernel", "bound": "hbm", "achieved": gbs,
+                                                    "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"], "traffic": None},
+                                       "cpu_baseline": {"clips_per_s": cpu_cps, "cores": 1, "kind": "port",
+                                                        "sample": f"{reps} clips, oracle/spec_oracle.py log_spectrogram (numpy rfft)"}}
+    except Exception as e:
+        out["spectrogram_b128_16k"] = {"error": repr(e)[:200]}
+
     # whole training step, config 2: stock-PyTorch backbones + fused head + Adam
     try:
         import types

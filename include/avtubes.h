@@ -200,6 +200,22 @@ int avt_mtc(const uint8_t* masks, int T, int32_t* pair_inter, int32_t* pair_unio
 int avt_video_metrics(const double* ciou, const uint8_t* masks, int V, int F,
                       int32_t* pair_inter, int32_t* pair_union, double* out, void* stream);
 
+/* ---- audio front-end ------------------------------------------------
+ * datasets/dataloader.py:86-96 for B clips in one launch: tile a short clip to n_keep samples
+ * (:88-91), clip to [-1, 1] (:92-93), scipy.signal.spectrogram(x, fs, nperseg=512, noverlap=1)
+ * (:94; hop 511, per-segment mean removal, window, one-sided 'density' PSD, 257 bins),
+ * log(S + log_eps) (:95) and Normalize(0, std) (:72,96).  fp64 arithmetic like scipy, fp32 out
+ * (the training loops call .float(), train_hardway_1frame.py:127).
+ *   samples  [B, stride] fp32 mono PCM in [-1, 1] (exact for <= 24-bit WAV)
+ *   lengths  [B] int32 valid samples per clip (tiled when < n_keep), or NULL = all n_keep
+ *   n_keep   samplerate * 10;   window [512] float64 (device), scipy's get_window(('tukey', .25), 512)
+ *   scale    1 / (samplerate * sum(window^2));   log_eps 1e-7;   std 12
+ *   out      [B, 257, T] fp32,  T = avt_spectrogram_frames(n_keep) = (n_keep - 1) / 511 */
+int avt_spectrogram_frames(int n_keep);
+int avt_log_spectrogram(const float* samples, const int32_t* lengths, int B, long long stride,
+                        int n_keep, const double* window, double scale, double log_eps, double std,
+                        float* out, int T, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
