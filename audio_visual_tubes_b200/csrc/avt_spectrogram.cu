@@ -3,11 +3,15 @@
 //     scipy.signal.spectrogram(x, fs, nperseg=512, noverlap=1)   (tukey(0.25) periodic window,
 //         detrend='constant', one-sided 'density' PSD: 257 bins, hop 511)
 //     log(S + 1e-7), ToTensor + Normalize(mean 0, std 12)  -> [1, 257, T], later .float()
-// One block = 8 consecutive segments of one clip: the 8 real 512-point transforms run as 4
-// complex radix-2 FFTs in shared memory (two real sequences per complex transform), all in
-// fp64 like scipy, and every frequency row gets 8 consecutive floats (one 32-byte sector).
-// HBM-bound: 4 B read per sample, 4 B written per bin.
+// One block = kSegs consecutive segments of one clip.  Two real segments ride one complex
+// 512-point transform (re = segment 2p, im = segment 2p + 1); a transform belongs to 64 threads
+// (two warps) that hold 8 points each in registers and run it as 8 x 8 x 8: three radix-8
+// butterflies with two conflict-free exchanges through shared memory (re / im planes of doubles,
+// padded), named barriers per warp pair instead of block-wide ones.  All arithmetic in fp64 like
+// scipy; every frequency row gets kSegs consecutive floats.
+// HBM-bound by design: 4 B read per sample, 4 B written per bin.
 #include "avt_common.cuh"
+#include <cstdlib>
 
 namespace avt {
 
@@ -16,90 +20,221 @@ namespace {
 constexpr int kSeg = 512;            // nperseg = nfft
 constexpr int kHop = 511;            // nperseg - noverlap
 constexpr int kBins = 257;
-constexpr int kSegPerBlock = 8;
-constexpr int kSpecThreads = 256;
+constexpr int kPlane = 580;          // 512 doubles + padding (every exchange layout fits 575; planes 4 banks apart)
+constexpr double kRh = 0.70710678118654752440;
 
-__global__ void __launch_bounds__(kSpecThreads)
+struct cd { double x, y; };
+__device__ __forceinline__ cd cadd(cd a, cd b) { return {a.x + b.x, a.y + b.y}; }
+__device__ __forceinline__ cd csub(cd a, cd b) { return {a.x - b.x, a.y - b.y}; }
+__device__ __forceinline__ cd cmul(cd a, cd b) { return {a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x}; }
+__device__ __forceinline__ cd mul_mi(cd a) { return {a.y, -a.x}; }                 // * (-i)
+
+// 8-point DFT (forward, W8 = exp(-2 pi i / 8)) in place; a[b] ends up holding Y[bitrev3(b)]
+__device__ __forceinline__ void dft8(cd (&a)[8]) {
+    cd u0 = cadd(a[0], a[4]), u4 = csub(a[0], a[4]);
+    cd u1 = cadd(a[1], a[5]), d1 = csub(a[1], a[5]);
+    cd u2 = cadd(a[2], a[6]), u6 = mul_mi(csub(a[2], a[6]));
+    cd u3 = cadd(a[3], a[7]), d3 = csub(a[3], a[7]);
+    cd u5 = {kRh * (d1.x + d1.y), kRh * (d1.y - d1.x)};                             // * W8^1
+    cd u7 = {kRh * (d3.y - d3.x), -kRh * (d3.x + d3.y)};                            // * W8^3
+    cd v0 = cadd(u0, u2), v2 = csub(u0, u2);
+    cd v1 = cadd(u1, u3), v3 = mul_mi(csub(u1, u3));
+    cd v4 = cadd(u4, u6), v6 = csub(u4, u6);
+    cd v5 = cadd(u5, u7), v7 = mul_mi(csub(u5, u7));
+    a[0] = cadd(v0, v1); a[1] = csub(v0, v1);      // Y0, Y4
+    a[2] = cadd(v2, v3); a[3] = csub(v2, v3);      // Y2, Y6
+    a[4] = cadd(v4, v5); a[5] = csub(v4, v5);      // Y1, Y5
+    a[6] = cadd(v6, v7); a[7] = csub(v6, v7);      // Y3, Y7
+}
+__device__ __forceinline__ constexpr int rev3(int q) { return ((q & 1) << 2) | (q & 2) | (q >> 2); }
+
+// a[rev3(q)] *= w^q for q = 1..7 (w^2, w^4 by squaring: at most three roundings deep)
+__device__ __forceinline__ void twiddle8(cd (&a)[8], cd w) {
+    const cd w2 = cmul(w, w), w3 = cmul(w2, w), w4 = cmul(w2, w2);
+    const cd w5 = cmul(w4, w), w6 = cmul(w4, w2), w7 = cmul(w4, w3);
+    a[rev3(1)] = cmul(a[rev3(1)], w);  a[rev3(2)] = cmul(a[rev3(2)], w2);
+    a[rev3(3)] = cmul(a[rev3(3)], w3); a[rev3(4)] = cmul(a[rev3(4)], w4);
+    a[rev3(5)] = cmul(a[rev3(5)], w5); a[rev3(6)] = cmul(a[rev3(6)], w6);
+    a[rev3(7)] = cmul(a[rev3(7)], w7);
+}
+
+__device__ __forceinline__ void pair_barrier(int id) {      // the two warps of one transform
+    asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
+}
+
+// log(x) for normal positive x from a per-block table: x = 2^e m, m in [1, 2); the top 7 mantissa
+// bits pick c = centre of m's 1/128 cell, table = (rc ~ 1/c, -log(rc)); r = m rc - 1 (|r| < 2^-7.9)
+// and log m = log1p(r) - log(rc) with log1p to r^7 (remainder < 1e-18); absolute error ~2e-16,
+// far below the fp32 rounding of the result.
+constexpr int kLogCells = 128;
+__device__ __forceinline__ double fast_log(double x, const double2* __restrict__ tab) {
+    const int hi = __double2hiint(x), lo = __double2loint(x);
+    const int e = (hi >> 20) - 1023;
+    const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, lo);
+    const double2 c = tab[(hi >> 13) & (kLogCells - 1)];
+    const double r = fma(m, c.x, -1.0);
+    double p = fma(r, 1.0 / 7.0, -1.0 / 6.0);
+    p = fma(p, r, 1.0 / 5.0);
+    p = fma(p, r, -1.0 / 4.0);
+    p = fma(p, r, 1.0 / 3.0);
+    p = fma(p, r, -0.5);
+    p = fma(p * r, r, r);
+    return fma((double)e, 0.69314718055994530942, c.y + p);
+}
+
+template <int kSegs>
+__global__ void __launch_bounds__(kSegs * 32)
 spectrogram_kernel(const float* __restrict__ samples, const int32_t* __restrict__ lengths,
                    long long stride, int n_keep, const double* __restrict__ window, double scale,
-                   double log_eps, double std, float* __restrict__ out, int T) {
-    __shared__ double2 z[kSegPerBlock / 2][kSeg];      // 32 KB: FFT p holds segments 2p (re), 2p+1 (im)
-    __shared__ double2 tw[kSeg / 2];                   // exp(-2 pi i j / 512)
+                   double log_eps, double inv_std, float* __restrict__ out, int T) {
+    constexpr int kFft = kSegs / 2;
+    __shared__ double sre[kFft][kPlane], sim[kFft][kPlane];
+    __shared__ double ssum[kSegs][2];
+    __shared__ double2 slog[kLogCells];
     const int clip = blockIdx.y;
-    const int t0 = blockIdx.x * kSegPerBlock;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t0 = blockIdx.x * kSegs;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int p = tid >> 6, u = tid & 63;                 // transform, thread within it
     const float* x = samples + (size_t)clip * stride;
-    const int L = lengths ? lengths[clip] : n_keep;    // shorter clips are tiled (dataloader.py:88-90)
-
-    {
-        double s, c;
-        sincospi(-(double)tid / 256.0, &s, &c);
-        tw[tid] = make_double2(c, s);
+    const int L = lengths ? lengths[clip] : n_keep;       // shorter clips are tiled (dataloader.py:88-90)
+    double* re = sre[p];
+    double* im = sim[p];
+    if (tid < kLogCells) {
+        const double rc = 1.0 / (1.0 + (tid + 0.5) * (1.0 / kLogCells));
+        slog[tid] = make_double2(rc, -log(rc));
     }
-    // warp w loads segment w: 16 samples per lane, clipped (dataloader.py:92-93); mean in fp64
+
+    // ---- load: thread u holds points u + 64 m of segments 2p (re) and 2p + 1 (im), clipped
+    // (dataloader.py:92-93); per-segment mean in fp64 (detrend='constant')
+    cd a[8];
     {
-        const int seg = warp, t = t0 + seg;
-        double v[16];
-        double sum = 0.0;
+        double s0 = 0.0, s1 = 0.0;
+        const int ta = t0 + 2 * p, tb = ta + 1;
+        if (L >= n_keep) {                                // block-uniform: a full 10 s clip, no tiling
+            const float* xa = x + (size_t)ta * kHop + u;
+            float fa[8], fb[8];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int n = t * kHop + lane + 32 * i;
-            float f = 0.f;
-            if (t < T) {
-                const int src = (L >= n_keep) ? n : n % L;
-                f = fminf(fmaxf(__ldg(x + src), -1.0f), 1.0f);
+            for (int m = 0; m < 8; ++m) {
+                fa[m] = ta < T ? __ldg(xa + 64 * m) : 0.f;
+                fb[m] = tb < T ? __ldg(xa + kHop + 64 * m) : 0.f;
             }
-            v[i] = (double)f;
-            sum += v[i];
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+                a[m].x = (double)fminf(fmaxf(fa[m], -1.0f), 1.0f);
+                a[m].y = (double)fminf(fmaxf(fb[m], -1.0f), 1.0f);
+                s0 += a[m].x; s1 += a[m].y;
+            }
+        } else {
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+                const int j = u + 64 * m;
+                const float fa = ta < T ? __ldg(x + (ta * kHop + j) % L) : 0.f;
+                const float fb = tb < T ? __ldg(x + (tb * kHop + j) % L) : 0.f;
+                a[m].x = (double)fminf(fmaxf(fa, -1.0f), 1.0f);
+                a[m].y = (double)fminf(fmaxf(fb, -1.0f), 1.0f);
+            }
+#pragma unroll
+            for (int m = 0; m < 8; ++m) { s0 += a[m].x; s1 += a[m].y; }
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        const double mean = sum / (double)kSeg;        // detrend='constant'
-        double* comp = reinterpret_cast<double*>(&z[seg >> 1][0]) + (seg & 1);
+        for (int o = 16; o > 0; o >>= 1) {
+            s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        }
+        const int half = (tid >> 5) & 1;
+        if (lane == 0) { ssum[2 * p][half] = s0; ssum[2 * p + 1][half] = s1; }
+        pair_barrier(1 + p);
+        const double m0 = (ssum[2 * p][0] + ssum[2 * p][1]) * (1.0 / kSeg);
+        const double m1 = (ssum[2 * p + 1][0] + ssum[2 * p + 1][1]) * (1.0 / kSeg);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int j = lane + 32 * i;
-            comp[2 * j] = (v[i] - mean) * window[j];
+        for (int m = 0; m < 8; ++m) {
+            const double w = __ldg(window + u + 64 * m);
+            a[m].x = (a[m].x - m0) * w;
+            a[m].y = (a[m].y - m1) * w;
+        }
+    }
+    // ---- pass 1: n = u + 64 m -> 8 sub-transforms q of length 64 over u, twiddle W512^(u q)
+    dft8(a);
+    {
+        cd w;
+        sincospi(-(double)u / 256.0, &w.y, &w.x);
+        twiddle8(a, w);
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {                         // layout 1: [q][u], rows padded to 72
+        re[72 * q + u] = a[rev3(q)].x;
+        im[72 * q + u] = a[rev3(q)].y;
+    }
+    pair_barrier(1 + p);
+    // ---- pass 2: thread (q, r) = (u / 8, u % 8) takes points r + 8 m of sub-transform q
+    {
+        const int q = u >> 3, r = u & 7;
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+            a[m].x = re[72 * q + r + 8 * m];
+            a[m].y = im[72 * q + r + 8 * m];
+        }
+        dft8(a);
+        cd w;
+        sincospi(-(double)r / 32.0, &w.y, &w.x);          // W64^r
+        twiddle8(a, w);
+        pair_barrier(1 + p);                              // everyone has read layout 1
+#pragma unroll
+        for (int q2 = 0; q2 < 8; ++q2) {                  // layout 2: row (8 q + q2) of 8, padded to 9
+            re[9 * (8 * q + q2) + r] = a[rev3(q2)].x;
+            im[9 * (8 * q + q2) + r] = a[rev3(q2)].y;
+        }
+    }
+    pair_barrier(1 + p);
+    // ---- pass 3: thread (q, q2) = (u / 8, u % 8) transforms its row -> X[q + 8 q2 + 64 r3]
+    {
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+            a[m].x = re[9 * u + m];
+            a[m].y = im[9 * u + m];
+        }
+        dft8(a);
+        pair_barrier(1 + p);                              // everyone has read layout 2
+        const int k0 = (u >> 3) + 8 * (u & 7);
+#pragma unroll
+        for (int r3 = 0; r3 < 8; ++r3) {                  // layout 3: natural order, 9 slots per 8
+            const int k = k0 + 64 * r3;
+            re[k + (k >> 3)] = a[rev3(r3)].x;
+            im[k + (k >> 3)] = a[rev3(r3)].y;
         }
     }
     __syncthreads();
-    // decimation-in-frequency radix-2, in place; X[k] ends at index bitrev9(k)
+    // ---- split the packed pairs, one-sided density PSD, log, normalise.  Thread = (segment s,
+    // bin k0 + 32 i): kSegs consecutive t per bin row, the even / odd split hoisted out of the loop
+    {
+        constexpr int kRows = kSegs * 32 / kSegs;         // bins per sweep = 32
+        const int sgm = tid % kSegs, t = t0 + sgm;
+        const double* pre = sre[sgm >> 1];
+        const double* pim = sim[sgm >> 1];
+        const bool odd = sgm & 1;
+        float* o = out + ((size_t)clip * kBins) * T + t;
+        if (t < T) {
 #pragma unroll 1
-    for (int h = kSeg / 2, shift = 0; h >= 1; h >>= 1, ++shift) {
-#pragma unroll
-        for (int p = 0; p < kSegPerBlock / 2; ++p) {
-            const int b = tid;                          // 256 butterflies per transform
-            const int j = b & (h - 1);
-            const int i0 = ((b - j) << 1) + j, i1 = i0 + h;
-            const double2 a = z[p][i0], c = z[p][i1];
-            const double2 w = tw[j << shift];
-            const double dr = a.x - c.x, di = a.y - c.y;
-            z[p][i0] = make_double2(a.x + c.x, a.y + c.y);
-            z[p][i1] = make_double2(dr * w.x - di * w.y, dr * w.y + di * w.x);
+            for (int k = tid / kSegs; k < kBins; k += kRows) {
+                const int kn = (kSeg - k) & (kSeg - 1);
+                const int ik = k + (k >> 3), in = kn + (kn >> 3);
+                const double zkx = pre[ik], zky = pim[ik], znx = pre[in], zny = pim[in];
+                // even: X = (Z[k] + conj(Z[N-k])) / 2;  odd: X = (Z[k] - conj(Z[N-k])) / (2i)
+                const double pr = odd ? zky + zny : zkx + znx;
+                const double pi = odd ? zkx - znx : zky - zny;
+                const double sc = (k != 0 && k != kSeg / 2) ? 0.5 * scale : 0.25 * scale;
+                o[(size_t)k * T] = (float)(fast_log(fma(pr * pr + pi * pi, sc, log_eps), slog) * inv_std);
+            }
         }
-        __syncthreads();
-    }
-    // split the packed pairs, one-sided density PSD, log, normalise; 8 consecutive t per bin
-    for (int idx = tid; idx < kBins * kSegPerBlock; idx += kSpecThreads) {
-        const int k = idx >> 3, s = idx & 7, t = t0 + s;
-        if (t >= T) continue;
-        const int p = s >> 1;
-        const double2 zk = z[p][__brev((unsigned)k) >> 23];
-        const double2 zn = z[p][__brev((unsigned)((kSeg - k) & (kSeg - 1))) >> 23];
-        double re, im;
-        if ((s & 1) == 0) {      // X1 = (Z[k] + conj(Z[N-k])) / 2
-            re = 0.5 * (zk.x + zn.x); im = 0.5 * (zk.y - zn.y);
-        } else {                 // X2 = (Z[k] - conj(Z[N-k])) / (2i)
-            re = 0.5 * (zk.y + zn.y); im = -0.5 * (zk.x - zn.x);
-        }
-        double psd = (re * re + im * im) * scale;
-        if (k != 0 && k != kSeg / 2) psd *= 2.0;
-        out[((size_t)clip * kBins + k) * T + t] = (float)(log(psd + log_eps) / std);
     }
 }
 
 }  // namespace
 }  // namespace avt
+
+#ifndef AVT_SPEC_SEGS
+#define AVT_SPEC_SEGS 8
+#endif
 
 using namespace avt;
 
@@ -118,9 +253,14 @@ extern "C" int avt_log_spectrogram(const float* samples, const int32_t* lengths,
     AVT_REQUIRE(T == avt_spectrogram_frames(n_keep), "avt_log_spectrogram: T=%d but %d samples give %d frames",
                 T, n_keep, avt_spectrogram_frames(n_keep));
     AVT_REQUIRE(std != 0.0, "avt_log_spectrogram: std is 0");
-    dim3 grid((T + kSegPerBlock - 1) / kSegPerBlock, B);
-    spectrogram_kernel<<<grid, kSpecThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        samples, lengths, stride, n_keep, window, scale, log_eps, std, out, T);
+    static const int segs = [] { const char* e = getenv("AVT_SPEC_SEGS"); return e ? atoi(e) : AVT_SPEC_SEGS; }();
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (segs == 4)
+        spectrogram_kernel<4><<<dim3((T + 3) / 4, B), 128, 0, st>>>(
+            samples, lengths, stride, n_keep, window, scale, log_eps, 1.0 / std, out, T);
+    else
+        spectrogram_kernel<8><<<dim3((T + 7) / 8, B), 256, 0, st>>>(
+            samples, lengths, stride, n_keep, window, scale, log_eps, 1.0 / std, out, T);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
