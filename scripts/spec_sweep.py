@@ -1,4 +1,4 @@
-"""Time avt_log_spectrogram (128 clips, 16 kHz, L2 flushed) -- used to pick segments per block."""
+"""Time avt_log_spectrogram (128 clips, 16 kHz, L2 flushed) -- the standalone timing loop the ncu captures in profiles/ run."""
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import spec_oracle as so
@@ -17,4 +17,4 @@ for _ in range(50):
 ts.sort(); ms = ts[len(ts) // 2]
 byt = bs * (fs * 10 * 4 + 257 * o.shape[-1] * 4)
 ref = so.log_spectrogram(wav[1].cpu().numpy(), fs)
-print(f"segs={os.environ.get('AVT_SPEC_SEGS','default')} fs={fs} ms={ms:.4f} (min {ts[0]:.4f}) GB/s={byt/ms/1e6:.0f} err={abs(o[1].cpu().numpy()-ref).max():.2e}")
+print(f"fs={fs} ms={ms:.4f} (min {ts[0]:.4f}) GB/s={byt/ms/1e6:.0f} err={abs(o[1].cpu().numpy()-ref).max():.2e}")
