@@ -521,6 +521,13 @@ def extras(avt, ev, _lib, cfg, dev, pk):
         tfr = (fs * 10 - 1) // 511
         bytes_alg = bs * (fs * 10 * 4 + 257 * tfr * 4)
         gbs = bytes_alg / (ms * 1e-3) / 1e9
+        # the same call from pinned host waveforms, spectrograms read back to the host
+        wav_h = wav.cpu().pin_memory()
+        spec_h = torch.empty(bs, 1, 257, tfr, dtype=torch.float32).pin_memory()
+
+        def spec_e2e():
+            spec_h.copy_(log_spectrogram(wav_h.to(dev, non_blocking=True), fs), non_blocking=True)
+        ms_e2e = timed(spec_e2e, 10, 3)
         t0 = time.perf_counter()
         w_np = wav[:4].cpu().numpy()
         reps = 0
@@ -528,6 +535,8 @@ def extras(avt, ev, _lib, cfg, dev, pk):
             so.log_spectrogram(w_np[reps % 4], fs); reps += 1
         cpu_cps = reps / (time.perf_counter() - t0)
         out["spectrogram_b128_16k"] = {"clips_per_s": bs / (ms * 1e-3), "ms": ms, "dtype": "f64 arithmetic, f32 out",
+                                       "e2e": {"clips_per_s": bs / (ms_e2e * 1e-3), "ms": ms_e2e, "h2d_bytes": bs * fs * 10 * 4,
+                                               "d2h_bytes": bs * 257 * tfr * 4},
                                        "roofline": {"kernel": "spectrogram_kernel", "bound": "hbm", "achieved": gbs,
                                                     "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
                                                     "traffic": 81938944 + 11092224, "traffic_source": "profiles/r1_ncu_spectrogram.txt (the 41 MB output stays in L2)",

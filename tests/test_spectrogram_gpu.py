@@ -90,3 +90,19 @@ def test_bad_arguments_raise():
     assert rc != 0
     with pytest.raises(RuntimeError):
         _lib.check(rc, "avt_log_spectrogram")
+
+
+def test_feeds_the_model_like_the_dataloader_output():
+    """waveform batch -> log_spectrogram -> AVENet.forward: the tensor takes the place of the
+    DataLoader's `spec` (train_hardway_1frame.py:127-129) without reshaping."""
+    import types
+    import audio_visual_tubes_b200 as avt
+    fs, b = 16000, 4
+    spec = avt.log_spectrogram(torch.from_numpy(so.synthetic_waveforms(b, fs, seed=2)).cuda(), fs)
+    args = types.SimpleNamespace(epsilon=0.65, epsilon2=0.4, tri_map=True, Neg=True)
+    torch.manual_seed(0)
+    net = avt.AVENet(args, False).cuda().eval()
+    with torch.no_grad():
+        A, logits, Pos, Neg = net(torch.randn(b, 3, 224, 224, device="cuda"), spec)
+    assert A.shape == (b, 1, 14, 14) and logits.shape == (b, b + 2)
+    assert torch.isfinite(logits).all() and torch.isfinite(A).all()
