@@ -45,6 +45,7 @@ SIGNATURES = {
     "avt_mtc": (_i, [_p, _i, _p, _p, _p, _p]),
     "avt_spectrogram_frames": (_i, [_i]),
     "avt_log_spectrogram": (_i, [_p, _p, _i, _ll, _i, _p, _d, _d, _d, _p, _i, _p]),
+    "avt_log_spectrogram_pcm16": (_i, [_p, _p, _i, _ll, _i, _p, _d, _d, _d, _p, _i, _p]),
     "avt_video_metrics": (_i, [_p, _p, _i, _i, _p, _p, _p, _p]),
 }
 

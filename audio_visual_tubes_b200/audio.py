@@ -37,14 +37,15 @@ def _window(device):
 
 
 def log_spectrogram(samples, samplerate: int, lengths=None):
-    """samples [B, >= min(length, 10 s)] fp32 mono waveforms on the GPU, ``samplerate`` as
+    """samples [B, >= min(length, 10 s)] mono waveforms on the GPU -- fp32 in [-1, 1], or int16 PCM
+    as stored in the WAV file (taken as sample / 32768, what ``sf.read`` returns) -- ``samplerate`` as
     ``sf.read`` reports it, ``lengths`` [B] valid samples per clip (shorter clips are tiled as
     dataloader.py:88-91 does; None = every row already holds 10 s).  Returns [B, 1, 257, T] fp32,
     the ``spectrogram`` tensor of ``__getitem__`` (dataloader.py:97) stacked by the DataLoader."""
     _lib.require_cuda(samples)
     lib = _lib.load()
-    if samples.dim() != 2 or samples.dtype != torch.float32:
-        raise ValueError("log_spectrogram: samples must be a [B, n] float32 tensor")
+    if samples.dim() != 2 or samples.dtype not in (torch.float32, torch.int16):
+        raise ValueError("log_spectrogram: samples must be a [B, n] float32 or int16 tensor")
     samples = samples.contiguous()
     b = samples.shape[0]
     n_keep = int(samplerate) * 10
@@ -62,8 +63,8 @@ def log_spectrogram(samples, samplerate: int, lengths=None):
     win, sumsq = _window(dev)
     out = torch.empty(b, 1, 257, t, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        rc = lib.avt_log_spectrogram(_lib.ptr(samples), _lib.ptr(lens), b, samples.stride(0), n_keep,
-                                     _lib.ptr(win), 1.0 / (samplerate * sumsq), LOG_EPS, STD,
-                                     _lib.ptr(out), t, _lib.stream_ptr())
+        fn = lib.avt_log_spectrogram if samples.dtype == torch.float32 else lib.avt_log_spectrogram_pcm16
+        rc = fn(_lib.ptr(samples), _lib.ptr(lens), b, samples.stride(0), n_keep, _lib.ptr(win),
+                1.0 / (samplerate * sumsq), LOG_EPS, STD, _lib.ptr(out), t, _lib.stream_ptr())
     _lib.check(rc, "avt_log_spectrogram")
     return out

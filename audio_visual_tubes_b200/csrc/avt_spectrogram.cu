@@ -85,9 +85,13 @@ __device__ __forceinline__ double fast_log_scaled(double x, const double2* __res
     return fma((double)e, g_ln2, fma(p, g, c.y));
 }
 
-template <int kSegs>
+// one sample as sf.read would return it: fp32 as is, 16-bit PCM divided by 32768 (exact in fp32)
+__device__ __forceinline__ float sample(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float sample(const int16_t* p) { return (float)__ldg(p) * (1.0f / 32768.0f); }
+
+template <int kSegs, typename TS>
 __global__ void __launch_bounds__(kSegs * 32)
-spectrogram_kernel(const float* __restrict__ samples, const int32_t* __restrict__ lengths,
+spectrogram_kernel(const TS* __restrict__ samples, const int32_t* __restrict__ lengths,
                    long long stride, int n_keep, const double* __restrict__ window, double scale,
                    double log_eps, double inv_std, float* __restrict__ out, int T) {
     constexpr int kFft = kSegs / 2;
@@ -98,7 +102,7 @@ spectrogram_kernel(const float* __restrict__ samples, const int32_t* __restrict_
     const int t0 = blockIdx.x * kSegs;
     const int tid = threadIdx.x, lane = tid & 31;
     const int p = tid >> 6, u = tid & 63;                 // transform, thread within it
-    const float* x = samples + (size_t)clip * stride;
+    const TS* x = samples + (size_t)clip * stride;
     const int L = lengths ? lengths[clip] : n_keep;       // shorter clips are tiled (dataloader.py:88-90)
     double* re = sre[p];
     double* im = sim[p];
@@ -114,12 +118,12 @@ spectrogram_kernel(const float* __restrict__ samples, const int32_t* __restrict_
         double s0 = 0.0, s1 = 0.0;
         const int ta = t0 + 2 * p, tb = ta + 1;
         if (L >= n_keep) {                                // block-uniform: a full 10 s clip, no tiling
-            const float* xa = x + (size_t)ta * kHop + u;
+            const TS* xa = x + (size_t)ta * kHop + u;
             float fa[8], fb[8];
 #pragma unroll
             for (int m = 0; m < 8; ++m) {
-                fa[m] = ta < T ? __ldg(xa + 64 * m) : 0.f;
-                fb[m] = tb < T ? __ldg(xa + kHop + 64 * m) : 0.f;
+                fa[m] = ta < T ? sample(xa + 64 * m) : 0.f;
+                fb[m] = tb < T ? sample(xa + kHop + 64 * m) : 0.f;
             }
 #pragma unroll
             for (int m = 0; m < 8; ++m) {
@@ -131,8 +135,8 @@ spectrogram_kernel(const float* __restrict__ samples, const int32_t* __restrict_
 #pragma unroll
             for (int m = 0; m < 8; ++m) {
                 const int j = u + 64 * m;
-                const float fa = ta < T ? __ldg(x + (ta * kHop + j) % L) : 0.f;
-                const float fb = tb < T ? __ldg(x + (tb * kHop + j) % L) : 0.f;
+                const float fa = ta < T ? sample(x + (ta * kHop + j) % L) : 0.f;
+                const float fb = tb < T ? sample(x + (tb * kHop + j) % L) : 0.f;
                 a[m].x = (double)fminf(fmaxf(fa, -1.0f), 1.0f);
                 a[m].y = (double)fminf(fmaxf(fb, -1.0f), 1.0f);
             }
@@ -245,22 +249,38 @@ extern "C" int avt_spectrogram_frames(int n_keep) {
     return n_keep < kSeg ? 0 : (n_keep - (kSeg - kHop)) / kHop;
 }
 
-extern "C" int avt_log_spectrogram(const float* samples, const int32_t* lengths, int B,
-                                   long long stride, int n_keep, const double* window, double scale,
-                                   double log_eps, double std, float* out, int T, void* stream) {
-    AVT_REQUIRE(B >= 0, "avt_log_spectrogram: B=%d", B);
+namespace {
+template <typename TS>
+int log_spectrogram(const char* who, const TS* samples, const int32_t* lengths, int B, long long stride,
+                    int n_keep, const double* window, double scale, double log_eps, double std,
+                    float* out, int T, void* stream) {
+    AVT_REQUIRE(B >= 0, "%s: B=%d", who, B);
     if (B == 0) return AVT_OK;
-    AVT_REQUIRE(samples && window && out, "avt_log_spectrogram: null pointer");
-    AVT_REQUIRE(n_keep >= kSeg && stride >= 1, "avt_log_spectrogram: n_keep=%d needs at least %d samples",
-                n_keep, kSeg);
-    AVT_REQUIRE(T == avt_spectrogram_frames(n_keep), "avt_log_spectrogram: T=%d but %d samples give %d frames",
+    AVT_REQUIRE(samples && window && out, "%s: null pointer", who);
+    AVT_REQUIRE(n_keep >= kSeg && stride >= 1, "%s: n_keep=%d needs at least %d samples", who, n_keep, kSeg);
+    AVT_REQUIRE(T == avt_spectrogram_frames(n_keep), "%s: T=%d but %d samples give %d frames", who,
                 T, n_keep, avt_spectrogram_frames(n_keep));
-    AVT_REQUIRE(std != 0.0, "avt_log_spectrogram: std is 0");
+    AVT_REQUIRE(std != 0.0, "%s: std is 0", who);
     // 8 segments per block: 4 segments halve the row runs (0.095 ms vs 0.078 ms for 128 clips at
     // 16 kHz), 16 (78 KB of opt-in shared memory, 512 threads) measured slower too: 0.086 ms
     constexpr int kSegs = 8;
-    spectrogram_kernel<kSegs><<<dim3((T + kSegs - 1) / kSegs, B), kSegs * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+    spectrogram_kernel<kSegs, TS><<<dim3((T + kSegs - 1) / kSegs, B), kSegs * 32, 0, static_cast<cudaStream_t>(stream)>>>(
         samples, lengths, stride, n_keep, window, scale, log_eps, 1.0 / std, out, T);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
+}
+}  // namespace
+
+extern "C" int avt_log_spectrogram(const float* samples, const int32_t* lengths, int B,
+                                   long long stride, int n_keep, const double* window, double scale,
+                                   double log_eps, double std, float* out, int T, void* stream) {
+    return log_spectrogram("avt_log_spectrogram", samples, lengths, B, stride, n_keep, window, scale,
+                           log_eps, std, out, T, stream);
+}
+
+extern "C" int avt_log_spectrogram_pcm16(const int16_t* samples, const int32_t* lengths, int B,
+                                         long long stride, int n_keep, const double* window, double scale,
+                                         double log_eps, double std, float* out, int T, void* stream) {
+    return log_spectrogram("avt_log_spectrogram_pcm16", samples, lengths, B, stride, n_keep, window, scale,
+                           log_eps, std, out, T, stream);
 }

@@ -215,6 +215,11 @@ int avt_spectrogram_frames(int n_keep);
 int avt_log_spectrogram(const float* samples, const int32_t* lengths, int B, long long stride,
                         int n_keep, const double* window, double scale, double log_eps, double std,
                         float* out, int T, void* stream);
+/* the same from 16-bit PCM as it sits in a WAV file: sample / 32768, what sf.read returns for
+ * PCM_16 (datasets/dataloader.py:86); half the bytes to upload and to read */
+int avt_log_spectrogram_pcm16(const int16_t* samples, const int32_t* lengths, int B, long long stride,
+                              int n_keep, const double* window, double scale, double log_eps, double std,
+                              float* out, int T, void* stream);
 
 #ifdef __cplusplus
 }

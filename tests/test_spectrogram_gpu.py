@@ -39,6 +39,20 @@ def test_short_clips_are_tiled_like_the_dataloader():
         assert np.abs(got[i] - want).max() <= TOL, f"clip {i} (length {n})"
 
 
+def test_pcm16_input_is_the_wav_file_read_by_soundfile():
+    """int16 samples / 32768 is what sf.read returns for a PCM_16 file (dataloader.py:86)."""
+    fs = 22050
+    lens = [fs * 10, 50001, 700]
+    x = so.synthetic_waveforms(3, fs, seed=8)
+    pcm = np.clip(np.round(x * 32768.0), -32768, 32767).astype(np.int16)
+    pcm[0, :100] = [-32768, 32767] * 50
+    got = _gpu(pcm, fs, lens)
+    for i, n in enumerate(lens):
+        want = so.log_spectrogram(pcm[i, :n].astype(np.float64) / 32768.0, fs)
+        assert np.abs(got[i] - want).max() <= TOL, f"clip {i}"
+    assert np.array_equal(got, _gpu((pcm.astype(np.float32) / 32768.0), fs, lens))
+
+
 def test_silence_and_full_scale_clip():
     fs = 16000
     x = np.zeros((3, fs * 10), np.float32)
