@@ -20,7 +20,7 @@ namespace {
 constexpr int kSeg = 512;            // nperseg = nfft
 constexpr int kHop = 511;            // nperseg - noverlap
 constexpr int kBins = 257;
-constexpr int kPlane = 580;          // 512 doubles + padding (every exchange layout fits 575; planes 4 banks apart)
+constexpr int kPlane = 644;          // 512 doubles + padding (layout 3 ends at 637; planes 4 banks apart)
 constexpr double kRh = 0.70710678118654752440;
 
 struct cd { double x, y; };
@@ -204,10 +204,10 @@ spectrogram_kernel(const TS* __restrict__ samples, const int32_t* __restrict__ l
         pair_barrier(1 + p);                              // everyone has read layout 2
         const int k0 = (u >> 3) + 8 * (u & 7);
 #pragma unroll
-        for (int r3 = 0; r3 < 8; ++r3) {                  // layout 3: natural order, 9 slots per 8
+        for (int r3 = 0; r3 < 8; ++r3) {                  // layout 3: natural order, 10 slots per 8
             const int k = k0 + 64 * r3;
-            re[k + (k >> 3)] = a[rev3(r3)].x;
-            im[k + (k >> 3)] = a[rev3(r3)].y;
+            re[k + 2 * (k >> 3)] = a[rev3(r3)].x;
+            im[k + 2 * (k >> 3)] = a[rev3(r3)].y;
         }
     }
     __syncthreads();
@@ -225,7 +225,7 @@ spectrogram_kernel(const TS* __restrict__ samples, const int32_t* __restrict__ l
 #pragma unroll 1
             for (int k = tid / kFft; k < kBins; k += kRows) {
                 const int kn = (kSeg - k) & (kSeg - 1);
-                const int ik = k + (k >> 3), in = kn + (kn >> 3);
+                const int ik = k + 2 * (k >> 3), in = kn + 2 * (kn >> 3);
                 const double zkx = pre[ik], zky = pim[ik], znx = pre[in], zny = pim[in];
                 // even: X = (Z[k] + conj(Z[N-k])) / 2;  odd: X = (Z[k] - conj(Z[N-k])) / (2i)
                 const double ar = zkx + znx, ai = zky - zny, br = zky + zny, bi = zkx - znx;
