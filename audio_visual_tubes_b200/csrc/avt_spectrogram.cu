@@ -58,6 +58,43 @@ __device__ __forceinline__ void twiddle8(cd (&a)[8], cd w) {
     a[rev3(7)] = cmul(a[rev3(7)], w7);
 }
 
+// exp(-2 pi i j / 512), j = 0..63, correctly rounded (generated with 50-digit arithmetic); pass 1 uses
+// entry u, pass 2 entry 8 r (W64^r)
+__device__ const double2 kW512[64] = {
+    {1.0, 0.0}, {0.9999247018391445, -0.012271538285719925},
+    {0.9996988186962042, -0.024541228522912288}, {0.9993223845883495, -0.03680722294135883},
+    {0.9987954562051724, -0.049067674327418015}, {0.9981181129001492, -0.06132073630220858},
+    {0.9972904566786902, -0.07356456359966743}, {0.996312612182778, -0.0857973123444399},
+    {0.9951847266721969, -0.0980171403295606}, {0.9939069700023561, -0.11022220729388306},
+    {0.99247953459871, -0.1224106751992162}, {0.99090263542778, -0.1345807085071262},
+    {0.989176509964781, -0.14673047445536175}, {0.9873014181578584, -0.15885814333386145},
+    {0.9852776423889412, -0.17096188876030122}, {0.9831054874312163, -0.18303988795514095},
+    {0.9807852804032304, -0.19509032201612828}, {0.9783173707196277, -0.20711137619221856},
+    {0.9757021300385286, -0.2191012401568698}, {0.9729399522055602, -0.2310581082806711},
+    {0.970031253194544, -0.2429801799032639}, {0.9669764710448521, -0.25486565960451457},
+    {0.9637760657954398, -0.26671275747489837}, {0.9604305194155658, -0.2785196893850531},
+    {0.9569403357322088, -0.2902846772544624}, {0.9533060403541939, -0.3020059493192281},
+    {0.9495281805930367, -0.31368174039889146}, {0.9456073253805213, -0.3253102921622629},
+    {0.9415440651830208, -0.33688985339222005}, {0.937339011912575, -0.34841868024943456},
+    {0.9329927988347388, -0.35989503653498817}, {0.9285060804732156, -0.37131719395183754},
+    {0.9238795325112867, -0.3826834323650898}, {0.9191138516900578, -0.3939920400610481},
+    {0.9142097557035307, -0.40524131400498986}, {0.9091679830905224, -0.4164295600976372},
+    {0.9039892931234433, -0.4275550934302821}, {0.8986744656939538, -0.43861623853852766},
+    {0.8932243011955153, -0.4496113296546066}, {0.8876396204028539, -0.46053871095824},
+    {0.881921264348355, -0.47139673682599764}, {0.8760700941954066, -0.4821837720791228},
+    {0.8700869911087115, -0.49289819222978404}, {0.8639728561215867, -0.5035383837257176},
+    {0.8577286100002721, -0.5141027441932218}, {0.8513551931052652, -0.524589682678469},
+    {0.8448535652497071, -0.5349976198870973}, {0.8382247055548381, -0.5453249884220465},
+    {0.8314696123025452, -0.5555702330196022}, {0.8245893027850253, -0.5657318107836132},
+    {0.8175848131515837, -0.5758081914178453}, {0.8104571982525948, -0.5857978574564389},
+    {0.8032075314806449, -0.5956993044924334}, {0.7958369046088836, -0.6055110414043255},
+    {0.7883464276266062, -0.6152315905806268}, {0.7807372285720945, -0.6248594881423863},
+    {0.773010453362737, -0.6343932841636455}, {0.765167265622459, -0.6438315428897915},
+    {0.7572088465064846, -0.6531728429537768}, {0.7491363945234594, -0.6624157775901718},
+    {0.7409511253549591, -0.6715589548470184}, {0.7326542716724128, -0.680600997795453},
+    {0.7242470829514669, -0.6895405447370669}, {0.7157308252838187, -0.6983762494089728},
+};
+
 __device__ __forceinline__ void pair_barrier(int id) {      // the two warps of one transform
     asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
 }
@@ -163,8 +200,8 @@ spectrogram_kernel(const TS* __restrict__ samples, const int32_t* __restrict__ l
     // ---- pass 1: n = u + 64 m -> 8 sub-transforms q of length 64 over u, twiddle W512^(u q)
     dft8(a);
     {
-        cd w;
-        sincospi(-(double)u / 256.0, &w.y, &w.x);
+        const double2 t = __ldg(&kW512[u]);
+        const cd w = {t.x, t.y};
         twiddle8(a, w);
     }
 #pragma unroll
@@ -182,8 +219,8 @@ spectrogram_kernel(const TS* __restrict__ samples, const int32_t* __restrict__ l
             a[m].y = im[72 * q + r + 8 * m];
         }
         dft8(a);
-        cd w;
-        sincospi(-(double)r / 32.0, &w.y, &w.x);          // W64^r
+        const double2 t = __ldg(&kW512[8 * r]);           // W64^r
+        const cd w = {t.x, t.y};
         twiddle8(a, w);
         pair_barrier(1 + p);                              // everyone has read layout 1
 #pragma unroll
