@@ -25,3 +25,13 @@ def test_window_is_scipys_default():
     assert np.array_equal(so.tukey_periodic(), signal.get_window(("tukey", 0.25), 512))
     from audio_visual_tubes_b200.audio import tukey_window_periodic
     assert np.array_equal(tukey_window_periodic(), so.tukey_periodic())
+
+
+def test_oracle_matches_committed_scipy_golden():
+    """tests/golden/make_golden_spectrogram.py ran dataloader.py:88-96 with scipy and froze the result."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "spectrogram_golden.npz"))
+    fs, wav = int(g["fs"]), so.synthetic_waveforms(2, int(g["fs"]), seed=int(g["seed"]), seconds=10.0)
+    for i, n in enumerate(g["lengths"]):
+        got = so.log_spectrogram(wav[i, :n], fs)[0][g["bins"]]
+        assert np.abs(got - g["spec"][i]).max() <= 1e-6

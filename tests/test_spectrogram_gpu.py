@@ -29,6 +29,17 @@ def test_ten_second_clips_match_oracle(fs):
         assert np.abs(got[i] - want).max() <= TOL
 
 
+def test_committed_scipy_golden():
+    """The frozen output of scipy.signal.spectrogram through dataloader.py:88-96
+    (tests/golden/make_golden_spectrogram.py); needs neither scipy nor the oracle's transform."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "spectrogram_golden.npz"))
+    fs = int(g["fs"])
+    wav = so.synthetic_waveforms(2, fs, seed=int(g["seed"]), seconds=10.0)
+    got = _gpu(wav, fs, [int(n) for n in g["lengths"]])
+    assert np.abs(got[:, 0][:, g["bins"]] - g["spec"]).max() <= TOL
+
+
 def test_short_clips_are_tiled_like_the_dataloader():
     fs = 16000
     lens = [fs * 10, 37123, 511, 1, 160001]
