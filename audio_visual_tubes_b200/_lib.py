@@ -12,8 +12,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libavtubes.so")
 
 PRECISION_FP32 = 0
-PRECISION_BF16 = 1
+PRECISION_F16 = 1
 GT_VGGSS, GT_FLICKR, GT_FLICKR_FRAME = 0, 1, 2
+EVAL_WORKSPACE_BYTES = 64
 
 _p = C.c_void_p
 _i = C.c_int
@@ -36,8 +37,8 @@ SIGNATURES = {
     "avt_head_forward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
                               _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
     "avt_head_backward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
-                               _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _z, _p]),
-    "avt_eval_maps": (_i, [_p, _i, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p]),
+                               _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
+    "avt_eval_maps": (_i, [_p, _i, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
     "avt_eval_stats": (_i, [_p, _i]),
     "avt_ciou_counts": (_i, [_p, _f, _p, _i, _i, _p, _p, _p, _p]),
     "avt_rasterise_gt": (_i, [_p, _p, _i, _i, _i, _p, _p]),

@@ -1,7 +1,7 @@
 // Shared helpers for the libavtubes kernels (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include "../../include/avtubes.h"
@@ -106,14 +106,24 @@ __device__ __forceinline__ float sigmoid_acc(float z) {
 // layout of the small per-call scratch at the head of every head workspace
 struct HeadScratch {
     unsigned int rows_done;      // last-block-done counter of the row-finish kernel
-    unsigned int pad[63];
+    unsigned int gmax_bits;      // backward: bits of max |cell gradient| bound (row_grad_kernel)
+    unsigned int pad[62];
 };
 
+// Power-of-two scale of the fp16 cell gradients G: bound * scale < 2^14 (the positive column adds
+// a second term of at most the same size, so |G * scale| < 2^15 < 65504), exact to undo.
+__host__ __device__ __forceinline__ int g_scale_exp(unsigned int bound_bits) {
+    if (bound_bits == 0u) return 0;
+    int se = 13 - ((int)(bound_bits >> 23) - 127);
+    return se < -100 ? -100 : (se > 100 ? 100 : se);
+}
+__device__ __forceinline__ float pow2i(int e) { return __int_as_float((e + 127) << 23); }
+
 // ---- kernel launchers implemented in the .cu files -------------------------------
-// prep: rnorm_v, A (positive map), msum (mean_c v_hat), optional bf16 K-major copy
+// prep: rnorm_v, A (positive map), msum (mean_c v_hat), optional fp16 K-major copy
 int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_idx, int col_offset,
                        int N_v, int N_a, int C, int P, float* rnorm_v, float* A, float* msum,
-                       __nv_bfloat16* vt_bf16, HeadScratch* scratch, cudaStream_t st);
+                       __half* vt_f16, HeadScratch* scratch, cudaStream_t st);
 int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int P, HeadParams hp,
                        float* Pos, float* Neg, float* weighted_A, float* logits,
                        float* loss_rows, float* loss_sum, HeadScratch* scratch, const int32_t* pos_idx,
@@ -124,7 +134,8 @@ int launch_sim_fp32(const float* v, const float* a_hat, const float* rnorm_v,
 int launch_row_grad(const float* A, const float* logits, const float* loss_rows,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int P, HeadParams hp,
                     float dloss_scale, const float* dlogits, const float* dA, float* gsim, float* GA,
-                    const float* sim, int col_mult, cudaStream_t st);
+                    const float* sim, int col_mult, const float* dloss_rows, const float* den,
+                    unsigned int* gmax_bits, cudaStream_t st);
 int launch_bwd_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, const float* gsim,
@@ -137,17 +148,18 @@ int launch_weighted_dv(const float* v, const float* rnorm_v, const float* msum, 
                        int N_v, int C, int P, float* dv, cudaStream_t st);
 int launch_dv_finish(const float* v, const float* rnorm_v, int N_v, int C, int P, float* dv,
                      cudaStream_t st);
-// tcgen05 path (avt_head_tc.cu): vt = normalised maps, bf16 [N_v*P (+slack)][C]; a_bf = audio
-// rows, bf16 [n_a_pad][C] (rows >= N_a zero)
-int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
+// tcgen05 path (avt_head_tc.cu): vt = normalised maps, fp16 [N_v*P (+slack)][C]; a_h = audio
+// rows, fp16 [n_a_pad][C] (rows >= N_a zero)
+int launch_sim_f16(const __half* vt, const __half* a_h,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
-int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, __nv_bfloat16* at_bf,
-                    __nv_bfloat16* g_bf, const float* a_hat, const float* rnorm_v,
+int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h, __half* at_h,
+                    __half* g_h, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C,
                     int P, HeadParams hp, const float* sim, const float* den, const float* gsim,
-                    const float* GA, float* dv, float* d_ahat, cudaStream_t st);
-int launch_audio_to_bf16(const float* a_hat, int N_a, int N_a_pad, int C, __nv_bfloat16* out,
+                    const float* GA, float* dv, float* d_ahat, const unsigned int* gmax_bits,
+                    cudaStream_t st);
+int launch_audio_to_f16(const float* a_hat, int N_a, int N_a_pad, int C, __half* out,
                          cudaStream_t st);
 
 }  // namespace avt

@@ -55,9 +55,8 @@ static_assert(kEvThreads == kDst, "rasterise_planes: one thread per destination 
 __device__ unsigned long long g_eval_stats[2];
 
 // Work tickets: maps are claimed one at a time (their cost varies, a static stride leaves a tail).
-// One slot per launch in flight, round robin; the last block out re-arms the slot.
-constexpr int kTicketSlots = 256;
-__device__ unsigned int g_eval_ticket[kTicketSlots][2];
+// The ticket word belongs to the CALL (caller-owned workspace, zeroed on the stream right before
+// the launch), so launches in flight, captured graphs and aborted kernels can not see each other.
 
 // Thread -> (column quad, row group): a warp walks a 128-pixel row segment, so its global accesses
 // are 512 / 128 contiguous bytes.  (An 8-quad x 4-strip patch per warp crosses the median contour
@@ -496,12 +495,11 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
                  const int16_t* __restrict__ boxes, const uint8_t* __restrict__ box_count,
                  int max_boxes, int gt_mode, float* __restrict__ up224, uint8_t* __restrict__ mask,
                  int32_t* __restrict__ inter_w, int32_t* __restrict__ union_w,
-                 double* __restrict__ ciou, int slot) {
+                 double* __restrict__ ciou, unsigned int* __restrict__ ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EvalSmem& S = *reinterpret_cast<EvalSmem*>(smem_raw);
     const int tid = threadIdx.x;
     if (tid < kStrips) S.geo[tid] = strip_pack(tid);           // published by the first barrier below
-    unsigned int* ticket = g_eval_ticket[slot];
     if (tid == 0) S.next_map = (int)atomicAdd(&ticket[0], 1u);
     __syncthreads();
     int map = S.next_map;
@@ -758,10 +756,6 @@ eval_maps_kernel(const float* __restrict__ maps14, int N, const uint8_t* __restr
         }
         map = next_map;
     }
-    if (tid == 0) {                                              // last block out re-arms the slot
-        __threadfence();
-        if (atomicAdd(&ticket[1], 1u) == gridDim.x - 1) { ticket[0] = 0u; ticket[1] = 0u; __threadfence(); }
-    }
 }
 
 // utils.py:241-274 / 276-309 -- boxes -> dense weights.  One block per map.
@@ -943,10 +937,11 @@ using namespace avt;
 extern "C" int avt_eval_maps(const float* maps14, int N, const uint8_t* gt_dense,
                              const int16_t* boxes, const uint8_t* box_count, int max_boxes,
                              int gt_mode, float* up224, uint8_t* mask, int32_t* inter_w,
-                             int32_t* union_w, double* ciou, void* stream) {
+                             int32_t* union_w, double* ciou, void* workspace, void* stream) {
     AVT_REQUIRE(N >= 0, "avt_eval_maps: N=%d", N);
     if (N == 0) return AVT_OK;
     AVT_REQUIRE(maps14 && inter_w && union_w && ciou, "avt_eval_maps: null pointer");
+    AVT_REQUIRE(workspace != nullptr, "avt_eval_maps: workspace is null (AVT_EVAL_WORKSPACE_BYTES device bytes)");
     AVT_REQUIRE(gt_dense || (boxes && box_count && max_boxes > 0 && max_boxes <= kMaxBoxesSmem),
                 "avt_eval_maps: need gt_dense, or boxes + box_count with 1 <= max_boxes <= %d",
                 kMaxBoxesSmem);
@@ -965,10 +960,10 @@ extern "C" int avt_eval_maps(const float* maps14, int N, const uint8_t* gt_dense
         AVT_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kEvThreads, smem));
         if (per_sm < 1) per_sm = 1;
         const int grid = N < sms * per_sm ? N : sms * per_sm;
-        static std::atomic<unsigned int> launches{0};
-        const int slot = (int)(launches.fetch_add(1u) % (unsigned int)kTicketSlots);
+        unsigned int* ticket = static_cast<unsigned int*>(workspace);
+        AVT_CHECK_CUDA(cudaMemsetAsync(ticket, 0, AVT_EVAL_WORKSPACE_BYTES, st));
         kernel<<<grid, kEvThreads, smem, st>>>(maps14, N, gt_dense, boxes, box_count, max_boxes, gt_mode,
-                                               up224, mask, inter_w, union_w, ciou, slot);
+                                               up224, mask, inter_w, union_w, ciou, ticket);
         return AVT_OK;
     };
     const int rc = gt_dense ? launch(eval_maps_kernel<true>) : launch(eval_maps_kernel<false>);

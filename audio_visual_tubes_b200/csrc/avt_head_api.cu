@@ -6,10 +6,10 @@ namespace avt {
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// Workspace layout (all offsets 1024-byte aligned).  The forward leaves the bf16 operand
+// Workspace layout (all offsets 1024-byte aligned).  The forward leaves the fp16 operand
 // copies in place; a backward called with the same workspace reuses them.
 struct HeadWorkspace {
-    size_t scratch, msum, gsim, ga, da_w, u_w, vt, a_bf, at_bf, g_bf, total;
+    size_t scratch, msum, gsim, ga, da_w, u_w, vt, a_h, at_h, g_h, total;
 };
 
 HeadWorkspace head_workspace_layout(int N_v, int N_a, int C, int P, int precision, int backward) {
@@ -18,15 +18,15 @@ HeadWorkspace head_workspace_layout(int N_v, int N_a, int C, int P, int precisio
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 1024); return o; };
     w.scratch = take(sizeof(HeadScratch));
     w.msum = take((size_t)N_v * P * sizeof(float));
-    w.gsim = w.ga = w.da_w = w.u_w = w.vt = w.a_bf = w.at_bf = w.g_bf = 0;
-    if (precision == AVT_PRECISION_BF16) {
+    w.gsim = w.ga = w.da_w = w.u_w = w.vt = w.a_h = w.at_h = w.g_h = 0;
+    if (precision == AVT_PRECISION_F16) {
         const size_t n_a_pad = (size_t)n_a_padded(N_a);
         // + one tile of slack rows so the last image's 208-row TMA box stays in bounds
-        w.vt = take(((size_t)N_v * P + 64) * C * sizeof(__nv_bfloat16));
-        w.a_bf = take(n_a_pad * C * sizeof(__nv_bfloat16));
+        w.vt = take(((size_t)N_v * P + 64) * C * sizeof(__half));
+        w.a_h = take(n_a_pad * C * sizeof(__half));
         if (backward) {
-            w.at_bf = take((size_t)C * n_a_pad * sizeof(__nv_bfloat16));
-            w.g_bf = take(((size_t)N_v * P + 128) * n_a_pad * sizeof(__nv_bfloat16));
+            w.at_h = take((size_t)C * n_a_pad * sizeof(__half));
+            w.g_h = take(((size_t)N_v * P + 128) * n_a_pad * sizeof(__half));
         }
     }
     if (backward) {
@@ -43,11 +43,11 @@ static int check_shapes(const char* fn, int N_v, int N_a, int C, int P, int prec
     AVT_REQUIRE(N_v > 0 && N_a > 0, "%s: N_v=%d N_a=%d must be positive", fn, N_v, N_a);
     AVT_REQUIRE(C > 0 && C % 64 == 0, "%s: C=%d must be a positive multiple of 64", fn, C);
     AVT_REQUIRE(P > 0 && P <= 256, "%s: P=%d must be in 1..256", fn, P);
-    AVT_REQUIRE(precision == AVT_PRECISION_FP32 || precision == AVT_PRECISION_BF16,
+    AVT_REQUIRE(precision == AVT_PRECISION_FP32 || precision == AVT_PRECISION_F16,
                 "%s: unknown precision %d", fn, precision);
-    if (precision == AVT_PRECISION_BF16) {
-        AVT_REQUIRE(P <= 208 && P % 4 == 0, "%s: bf16 path needs P <= 208 and P %% 4 == 0 (P=%d)", fn, P);
-        AVT_REQUIRE(C % 64 == 0 && C <= 4096, "%s: bf16 path needs C %% 64 == 0", fn);
+    if (precision == AVT_PRECISION_F16) {
+        AVT_REQUIRE(P <= 208 && P % 4 == 0, "%s: fp16 path needs P <= 208 and P %% 4 == 0 (P=%d)", fn, P);
+        AVT_REQUIRE(C % 64 == 0 && C <= 4096, "%s: fp16 path needs C %% 64 == 0", fn);
     }
     return AVT_OK;
 }
@@ -99,18 +99,18 @@ extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int
         if (rc != AVT_OK) return rc;
     } else {
         if (!avt_device_ok()) {
-            set_error("avt_head_forward: the bf16 tcgen05 path needs an sm_100 device");
+            set_error("avt_head_forward: the fp16 tcgen05 path needs an sm_100 device");
             return AVT_ERR_UNSUPPORTED;
         }
-        __nv_bfloat16* vt = reinterpret_cast<__nv_bfloat16*>(ws + w.vt);
-        __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
+        __half* vt = reinterpret_cast<__half*>(ws + w.vt);
+        __half* a_h = reinterpret_cast<__half*>(ws + w.a_h);
         const int n_a_pad = n_a_padded(N_a);
-        rc = launch_audio_to_bf16(a_hat, N_a, n_a_pad, C, a_bf, st);
+        rc = launch_audio_to_f16(a_hat, N_a, n_a_pad, C, a_h, st);
         if (rc != AVT_OK) return rc;
         rc = launch_prep_visual(v, a_hat, pos_idx, col_offset, N_v, N_a, C, P, rnorm_v, A, msum, vt,
                                 scratch, st);
         if (rc != AVT_OK) return rc;
-        rc = launch_sim_bf16(vt, a_bf, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den, st);
+        rc = launch_sim_f16(vt, a_h, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den, st);
         if (rc != AVT_OK) return rc;
     }
     return launch_finish_rows(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A, logits, loss_rows,
@@ -122,7 +122,8 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
                                  float tau, float temp, float mask_scale, int trimap, int use_neg,
                                  int precision, int col_mult, const float* A, const float* logits,
                                  const float* loss_rows, const float* rnorm_v, const float* sim,
-                                 const float* den, float dloss_scale, const float* dlogits,
+                                 const float* den, float dloss_scale, const float* dloss_rows,
+                                 const float* dlogits,
                                  const float* dA, const float* dWeighted, float* dv,
                                  float* d_ahat, void* workspace,
                                  size_t workspace_bytes, void* stream) {
@@ -152,8 +153,14 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
         if (rc != AVT_OK) return rc;
         dA = da_w;
     }
+    HeadScratch* scratch = reinterpret_cast<HeadScratch*>(ws + w.scratch);
+    unsigned int* gmax_bits = nullptr;
+    if (precision == AVT_PRECISION_F16) {          // bound of the cell gradients -> fp16 scale of G
+        gmax_bits = &scratch->gmax_bits;
+        AVT_CHECK_CUDA(cudaMemsetAsync(gmax_bits, 0, sizeof(unsigned int), st));
+    }
     rc = launch_row_grad(A, logits, loss_rows, pos_idx, col_offset, N_v, N_a, P, hp, dloss_scale,
-                         dlogits, dA, gsim, GA, sim, col_mult, st);
+                         dlogits, dA, gsim, GA, sim, col_mult, dloss_rows, den, gmax_bits, st);
     if (rc != AVT_OK) return rc;
     AVT_CHECK_CUDA(cudaMemsetAsync(d_ahat, 0, (size_t)N_a * C * sizeof(float), st));
     if (precision == AVT_PRECISION_FP32) {
@@ -166,16 +173,16 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
         return launch_weighted_dv(v, rnorm_v, msum, u_w, N_v, C, P, dv, st);
     }
     if (!avt_device_ok()) {
-        set_error("avt_head_backward: the bf16 tcgen05 path needs an sm_100 device");
+        set_error("avt_head_backward: the fp16 tcgen05 path needs an sm_100 device");
         return AVT_ERR_UNSUPPORTED;
     }
     const int n_a_pad = n_a_padded(N_a);
-    __nv_bfloat16* vt = reinterpret_cast<__nv_bfloat16*>(ws + w.vt);
-    __nv_bfloat16* a_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.a_bf);
-    __nv_bfloat16* at_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.at_bf);
-    __nv_bfloat16* g_bf = reinterpret_cast<__nv_bfloat16*>(ws + w.g_bf);
-    rc = launch_bwd_bf16(v, vt, a_bf, at_bf, g_bf, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
-                         n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, st);
+    __half* vt = reinterpret_cast<__half*>(ws + w.vt);
+    __half* a_h = reinterpret_cast<__half*>(ws + w.a_h);
+    __half* at_h = reinterpret_cast<__half*>(ws + w.at_h);
+    __half* g_h = reinterpret_cast<__half*>(ws + w.g_h);
+    rc = launch_bwd_f16(v, vt, a_h, at_h, g_h, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
+                         n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, gmax_bits, st);
     if (rc != AVT_OK || !dWeighted) return rc;
     return launch_weighted_dv(v, rnorm_v, msum, u_w, N_v, C, P, dv, st);
 }

@@ -136,12 +136,19 @@ __device__ __forceinline__ float block_sum_rg(float x, float* s_tmp) {
 __global__ void __launch_bounds__(kRowGradThreads)
 row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
                 const float* __restrict__ loss_rows, const int32_t* __restrict__ pos_idx,
-                int col_offset, int N_a, int P, HeadParams hp, float dloss_scale,
+                int col_offset, int N_a, int P, HeadParams hp, float dloss_scale_all,
                 const float* __restrict__ dlogits, const float* __restrict__ dA,
                 float* __restrict__ gsim, float* __restrict__ GA, const float* __restrict__ sim,
-                int col_mult) {
+                int col_mult, const float* __restrict__ dloss_rows, const float* __restrict__ den,
+                unsigned int* __restrict__ gmax_bits) {
     __shared__ float s_tmp[kRowGradThreads / 32];
     const int n = blockIdx.x;
+    // upstream gradient of this row's loss: the uniform scalar plus an optional per-row term
+    // (loss_rows.mean().backward() and friends never leave the library for a softmax)
+    const float dloss_scale = dloss_scale_all + (dloss_rows ? dloss_rows[n] : 0.f);
+    // bound of |cell gradient| for the fp16 scale of G: |G| <= |gsim/den| (1 + 0.5/tau) (+ |GA|)
+    const float gfac = 1.0f + 0.5f / hp.tau;
+    float mx = 0.f;
     const int L = N_a + 1 + (hp.use_neg ? 1 : 0);
     const float* lg = logits + (size_t)n * L;
     const float lse = loss_rows[n] + lg[0];
@@ -163,6 +170,7 @@ row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
             }
             if (dlogits) g += dlogits[(size_t)n * L + 1 + k];
             gsim[(size_t)n * N_a + k] = g * itemp;
+            if (den) mx = fmaxf(mx, fabsf(g * itemp / den[(size_t)n * N_a + k]) * gfac);
         }
     } else {
         for (int k = threadIdx.x; k < N_a; k += kRowGradThreads) {
@@ -170,6 +178,7 @@ row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
             if (dlogits) g += dlogits[(size_t)n * L + 1 + k];
             float m = (k == pos) ? (1.0f - hp.mask_scale) : 1.0f;
             gsim[(size_t)n * N_a + k] = g * m * itemp;
+            if (den) mx = fmaxf(mx, fabsf(g * m * itemp / den[(size_t)n * N_a + k]) * gfac);
         }
     }
     float g1 = dloss_scale * (expf(lg[0] - lse) - 1.0f);
@@ -217,17 +226,32 @@ row_grad_kernel(const float* __restrict__ A, const float* __restrict__ logits,
         g += g2 * (w2 - (a - sim2) * w2 * (1.0f - w2) * itau) / sn;
         if (dA) g += dA[(size_t)n * P + p];
         GA[(size_t)n * P + p] = g;
+        mx = fmaxf(mx, fabsf(g));
+    }
+    if (gmax_bits) {                                     // non-negative floats order like their bits
+        mx = warp_max(mx);
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) s_tmp[threadIdx.x >> 5] = mx;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float t = s_tmp[0];
+#pragma unroll
+            for (int i = 1; i < kRowGradThreads / 32; ++i) t = fmaxf(t, s_tmp[i]);
+            if (!(t <= 3.0e38f)) t = 3.0e38f;            // NaN / Inf upstream: keep the scale finite
+            atomicMax(gmax_bits, __float_as_uint(t));
+        }
     }
 }
 
 int launch_row_grad(const float* A, const float* logits, const float* loss_rows,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int P, HeadParams hp,
                     float dloss_scale, const float* dlogits, const float* dA, float* gsim, float* GA,
-                    const float* sim, int col_mult, cudaStream_t st) {
+                    const float* sim, int col_mult, const float* dloss_rows, const float* den,
+                    unsigned int* gmax_bits, cudaStream_t st) {
     ProfScope _ps(kProfRowGrad, st);
     row_grad_kernel<<<N_v, kRowGradThreads, 0, st>>>(A, logits, loss_rows, pos_idx, col_offset, N_a,
                                                      P, hp, dloss_scale, dlogits, dA, gsim, GA, sim,
-                                                     col_mult);
+                                                     col_mult, dloss_rows, den, gmax_bits);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
@@ -262,7 +286,7 @@ bwd_fp32_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
     __syncthreads();
 
     // S for this block's 16 audio rows, then the pooled sim / den recomputed in fp32 here
-    // (self-consistent gradient; the saved forward values may come from the bf16 path)
+    // (self-consistent gradient; the saved forward values may come from the fp16 path)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const float itau = 1.0f / hp.tau;
     float S[kKT], W[kKT];

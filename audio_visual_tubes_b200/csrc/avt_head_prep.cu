@@ -1,5 +1,5 @@
 // Row-wise pieces of the head: audio normalisation (+ adjoint), the single pass over
-// the visual maps that yields 1/||v||, the positive map A and the bf16 K-major copy
+// the visual maps that yields 1/||v||, the positive map A and the fp16 K-major copy
 // for the tensor-core contraction, and the per-row finish (tri-map, sim1/sim2,
 // weighted_A, cross-entropy).  HBM-bound kernels: coalesced along P, 16 independent
 // loads in flight per thread.
@@ -39,26 +39,26 @@ __global__ void audio_normalize_bwd_kernel(const float* __restrict__ a_hat,
     for (int c = lane; c < C; c += 32) da[(size_t)row * C + c] = rn * (g[c] - h[c] * dot);
 }
 
-__global__ void audio_to_bf16_kernel(const float* __restrict__ a_hat, int N_a, int N_a_pad, int C,
-                                     __nv_bfloat16* __restrict__ out) {
+__global__ void audio_to_f16_kernel(const float* __restrict__ a_hat, int N_a, int N_a_pad, int C,
+                                     __half* __restrict__ out) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     size_t total = (size_t)N_a_pad * C;
     if (i >= total) return;
     size_t row = i / C;
-    out[i] = __float2bfloat16_rn(row < (size_t)N_a ? a_hat[i] : 0.f);
+    out[i] = __float2half_rn(row < (size_t)N_a ? a_hat[i] : 0.f);
 }
 
-int launch_audio_to_bf16(const float* a_hat, int N_a, int N_a_pad, int C, __nv_bfloat16* out,
+int launch_audio_to_f16(const float* a_hat, int N_a, int N_a_pad, int C, __half* out,
                          cudaStream_t st) {
     size_t total = (size_t)N_a_pad * C;
-    audio_to_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(a_hat, N_a, N_a_pad, C, out);
+    audio_to_f16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(a_hat, N_a, N_a_pad, C, out);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
 
 // ------------------------------------------------------------------ visual prep pass
 // model.py:117 (norm over C per position), :124 (positive map), :150 (mean_c of the
-// normalised map) and, for the tensor-core path, v_hat as bf16 K-major [n][p][c].
+// normalised map) and, for the tensor-core path, v_hat as fp16 K-major [n][p][c].
 // ONE read of v: a block owns 32 positions of one image, its 16 warps own C/16 channels
 // each, and every thread keeps its <= 32 values in registers between the reduction over
 // the channels and the normalised write-out (the earlier two-sweep version re-read v from
@@ -70,12 +70,12 @@ constexpr int kPrepMaxCpw = 32;                  // channels per warp, C <= 512
 
 // kC / kP: compile-time C and P of the reference's shapes (512 channels, 14 x 14 positions) so that
 // every guard folds and every load / store offset is an immediate; 0 = take the run-time value.
-template <bool kWriteBf16, int kC, int kP>
+template <bool kWriteF16, int kC, int kP>
 __global__ void __launch_bounds__(kPrepThreads, 2)
 prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
                    const int32_t* __restrict__ pos_idx, int col_offset, int N_a, int C_rt, int P_rt,
                    float* __restrict__ rnorm_v, float* __restrict__ A, float* __restrict__ msum,
-                   __nv_bfloat16* __restrict__ vt, HeadScratch* scratch) {
+                   __half* __restrict__ vt, HeadScratch* scratch) {
     const int C = kC ? kC : C_rt, P = kP ? kP : P_rt;
     extern __shared__ float smem[];
     float* s_a = smem;                       // [C]  positive audio row
@@ -127,9 +127,9 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
         A[o] = t1 * rn;
         msum[o] = t2 * rn / (float)C;
     }
-    if (kWriteBf16) {
+    if (kWriteF16) {
         // transpose through shared memory so the K-major rows leave as 512-byte bursts:
-        // tile[p][c] bf16 with a 16-byte pad per row (16-byte accesses stay conflict-free)
+        // tile[p][c] fp16 with a 16-byte pad per row (16-byte accesses stay conflict-free)
         uint8_t* s_tile = reinterpret_cast<uint8_t*>(s_red + 3 * kPrepWarps * 32);
         const int pitch = C * 2 + 16;
 #pragma unroll
@@ -138,7 +138,7 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
                 uint32_t wds[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    __nv_bfloat162 h = __floats2bfloat162_rn(x[i + 2 * e] * rn, x[i + 2 * e + 1] * rn);
+                    __half2 h = __floats2half2_rn(x[i + 2 * e] * rn, x[i + 2 * e + 1] * rn);
                     wds[e] = *reinterpret_cast<uint32_t*>(&h);
                 }
                 if (cpw % 8 == 0) {
@@ -164,16 +164,16 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
 
 int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_idx, int col_offset,
                        int N_v, int N_a, int C, int P, float* rnorm_v, float* A, float* msum,
-                       __nv_bfloat16* vt_bf16, HeadScratch* scratch, cudaStream_t st) {
+                       __half* vt_f16, HeadScratch* scratch, cudaStream_t st) {
     ProfScope _ps(kProfPrep, st);
     AVT_REQUIRE(C % 64 == 0 && C <= kPrepWarps * kPrepMaxCpw, "prep: C=%d must be a multiple of 64, <= 512", C);
     dim3 grid((P + 31) / 32, N_v);
-    size_t smem = (size_t)(C + 3 * kPrepWarps * 32) * sizeof(float) + (vt_bf16 ? (size_t)32 * (C * 2 + 16) : 0);
+    size_t smem = (size_t)(C + 3 * kPrepWarps * 32) * sizeof(float) + (vt_f16 ? (size_t)32 * (C * 2 + 16) : 0);
     const bool ref_shape = (C == 512 && P == 196);
 #define AVT_PREP(BF, KC, KP)                                                                        \
     prep_visual_kernel<BF, KC, KP><<<grid, kPrepThreads, smem, st>>>(v, a_hat, pos_idx, col_offset, N_a, C, P, \
-                                                                     rnorm_v, A, msum, vt_bf16, scratch)
-    if (vt_bf16) { if (ref_shape) AVT_PREP(true, 512, 196); else AVT_PREP(true, 0, 0); }
+                                                                     rnorm_v, A, msum, vt_f16, scratch)
+    if (vt_f16) { if (ref_shape) AVT_PREP(true, 512, 196); else AVT_PREP(true, 0, 0); }
     else { if (ref_shape) AVT_PREP(false, 512, 196); else AVT_PREP(false, 0, 0); }
 #undef AVT_PREP
     AVT_LAUNCH_CHECK();

@@ -1,4 +1,4 @@
-// AVT_PRECISION_BF16: the all-pairs contraction S[n,k,p] = <v_hat[n,:,p], a_hat[k,:]>
+// AVT_PRECISION_F16: the all-pairs contraction S[n,k,p] = <v_hat[n,:,p], a_hat[k,:]>
 // (model.py:125) on the 5th-generation tensor cores, with the tri-map sigmoid and the masked
 // pooling (model.py:135,140) applied straight out of tensor memory -- S never reaches HBM.
 //
@@ -7,9 +7,9 @@
 // pair and the pooling over p is a private loop over TMEM columns: no cross-thread
 // reduction anywhere.
 //
-//   operands   A = a_hat as bf16 [n_a_pad][C]   K-major, 128-byte swizzle, RESIDENT in shared
+//   operands   A = a_hat as fp16 [n_a_pad][C]   K-major, 128-byte swizzle, RESIDENT in shared
 //                  memory for all images a block visits (128 KB)
-//              B = v_hat as bf16 [N_v*P][C]     K-major, streamed by TMA, 3 stages x 26 KB;
+//              B = v_hat as fp16 [N_v*P][C]     K-major, streamed by TMA, 3 stages x 26 KB;
 //                  rows 196..207 of a box belong to the next image (or are zero-filled past
 //                  the end) and land in accumulator columns nobody reads
 //   TMEM       2 accumulators x 256 columns: the epilogue of tile i overlaps the MMAs of i+1
@@ -49,7 +49,7 @@ constexpr float kTinyDen = 9.313225746154785e-10f;      // 2^-30
 
 template <bool kGrad, bool kExact, int N>
 __device__ __forceinline__ void cell_chunk(const uint32_t (&r)[N], const CellCtx& cx, float& num,
-                                           float& dn, __nv_bfloat16* gp, uint32_t pitch) {
+                                           float& dn, __half* gp, uint32_t pitch) {
 #pragma unroll
     for (int i = 0; i < N; i += 2) {
         const float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
@@ -67,8 +67,8 @@ __device__ __forceinline__ void cell_chunk(const uint32_t (&r)[N], const CellCtx
         if (kGrad) {
             const float g0 = (cx.coef * w0) * fmaf(s0 - cx.sm, fmaf(-w0, cx.itau, cx.itau), 1.0f);
             const float g1 = (cx.coef * w1) * fmaf(s1 - cx.sm, fmaf(-w1, cx.itau, cx.itau), 1.0f);
-            gp[(uint32_t)i * pitch] = __float2bfloat16_rn(g0);
-            gp[(uint32_t)(i + 1) * pitch] = __float2bfloat16_rn(g1);
+            gp[(uint32_t)i * pitch] = __float2half_rn(g0);
+            gp[(uint32_t)(i + 1) * pitch] = __float2half_rn(g1);
         } else {
             dn += w0 + w1;
             num = fmaf(w0, s0, num);
@@ -80,7 +80,7 @@ __device__ __forceinline__ void cell_chunk(const uint32_t (&r)[N], const CellCtx
 // all columns [c_begin, c_end) of one TMEM lane (c_end - c_begin a multiple of 4)
 template <bool kGrad, bool kExact>
 __device__ __forceinline__ void cell_sweep(uint32_t taddr, int c_begin, int c_end, const CellCtx& cx,
-                                           float& num, float& dn, __nv_bfloat16* gout, uint32_t pitch) {
+                                           float& num, float& dn, __half* gout, uint32_t pitch) {
     int c = c_begin;
     for (; c + 32 <= c_end; c += 32) {
         uint32_t r[32];
@@ -99,16 +99,16 @@ __device__ __forceinline__ void cell_sweep(uint32_t taddr, int c_begin, int c_en
 // kGrad = false: forward (writes sim / den / logits).
 // kGrad = true : backward stage 1.  The same contraction is recomputed and the epilogue turns
 //   every cell into its gradient  G = gsim/den * w (1 + (S - sim)(1 - w)/tau)  (+ GA on the
-//   positive column), stored as bf16 in G[n*P + p][k] (row pitch n_a_pad) --
+//   positive column), stored as fp16 in G[n*P + p][k] (row pitch n_a_pad) --
 //   the K-major A operand of the dv contraction and the MN-major A operand of the d_ahat one.
 template <bool kGrad>
 __global__ void __launch_bounds__(kTcThreads, 1)
-sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                 const int32_t* __restrict__ pos_idx, int col_offset, int N_v, int N_a, int n_mt,
                 int groups, int KC, int P, HeadParams hp, int L, float* __restrict__ logits,
                 float* __restrict__ sim, float* __restrict__ den,
                 const float* __restrict__ gsim, const float* __restrict__ GA,
-                __nv_bfloat16* __restrict__ G, int n_a_pad) {
+                __half* __restrict__ G, int n_a_pad, const unsigned int* __restrict__ gmax_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sA = base;
@@ -161,7 +161,7 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         }
     } else if (warp == 1) {
         if (lane == 0) {                                 // ---------------- MMA issuer
-            const uint32_t idesc = make_idesc_bf16(kBM, kBN, 0, 0);
+            const uint32_t idesc = make_idesc_f16(kBM, kBN, 0, 0);
             int stage = 0; uint32_t phase = 0, a_par = 0;
             uint32_t tile = 0;
             for (int mt = mt0; mt < n_mt; mt += mt_step) {
@@ -181,7 +181,7 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         for (int k = 0; k < kBK / 16; ++k) {
                             const uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
                             const uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
-                            umma_bf16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                            umma_f16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
                         }
                         umma_commit(&empty_b[stage]);    // frees the stage once these MMAs retire
                         if (++stage == kStagesB) { stage = 0; phase ^= 1; }
@@ -201,6 +201,10 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         const int row = q * 32 + lane;
         const float c1 = -kLog2e / hp.tau, c0 = hp.eps * kLog2e / hp.tau;
         const float itemp = 1.0f / hp.temp, itau = 1.0f / hp.tau;
+        // fp16 keeps 11 significant bits but only 2^-14..2^15 of range: the cell gradients are
+        // stored times a power of two derived from their bound (row_grad_kernel), undone exactly
+        // by the two contractions that consume them
+        const float gscale = kGrad ? pow2i(g_scale_exp(__ldg(gmax_bits))) : 1.0f;
         uint32_t tile = 0;
         for (int mt = mt0; mt < n_mt; mt += mt_step) {
             const int k = mt * kBM + row;
@@ -225,12 +229,12 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     if (k < N_a) {
                         dnk = nx_den;
                         cx.sm = nx_sim;
-                        cx.coef = nx_gs / dnk;
+                        cx.coef = nx_gs / dnk * gscale;
                     }
                     exact = __any_sync(0xffffffffu, dnk < kTinyDen);
                     fetch(n + groups);
                 }
-                __nv_bfloat16* gout = G + (size_t)n * P * n_a_pad + k;
+                __half* gout = G + (size_t)n * P * n_a_pad + k;
                 const uint32_t pitch = (uint32_t)n_a_pad;
                 mbar_wait(&tmem_full[buf], use & 1u);
                 tc_fence_after();
@@ -249,10 +253,10 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     if (m) {
                         __syncwarp();
                         const int kp = mt * kBM + q * 32 + (__ffs(m) - 1);
-                        __nv_bfloat16* gcol = G + (size_t)n * P * n_a_pad + kp;
+                        __half* gcol = G + (size_t)n * P * n_a_pad + kp;
                         for (int pp = c_begin + lane; pp < c_end; pp += 32) {
-                            __nv_bfloat16* a = gcol + (uint32_t)pp * pitch;
-                            *a = __float2bfloat16_rn(__bfloat162float(*a) + GA[(size_t)n * P + pp]);
+                            __half* a = gcol + (uint32_t)pp * pitch;
+                            *a = __float2half_rn(fmaf(GA[(size_t)n * P + pp], gscale, __half2float(*a)));
                         }
                     }
                 }
@@ -280,18 +284,19 @@ sim_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }
 }
 
-static int launch_sim_tc(bool grad, const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
+static int launch_sim_tc(bool grad, const __half* vt, const __half* a_h,
                          const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                          HeadParams hp, float* logits, float* sim, float* den, const float* gsim,
-                         const float* GA, __nv_bfloat16* G, int n_a_pad, cudaStream_t st) {
-    AVT_REQUIRE(C % kBK == 0 && C <= kMaxKC * kBK, "bf16 head: C=%d must be a multiple of 64, <= 512", C);
-    AVT_REQUIRE(P % 4 == 0 && P <= kBN, "bf16 head: P=%d must be a multiple of 4, <= 208", P);
+                         const float* GA, __half* G, int n_a_pad, const unsigned int* gmax_bits,
+                         cudaStream_t st) {
+    AVT_REQUIRE(C % kBK == 0 && C <= kMaxKC * kBK, "fp16 head: C=%d must be a multiple of 64, <= 512", C);
+    AVT_REQUIRE(P % 4 == 0 && P <= kBN, "fp16 head: P=%d must be a multiple of 4, <= 208", P);
     // backward: every column of G up to n_a_pad must be written (pad columns get zeros)
     const int n_mt = grad ? n_a_pad / kBM : (N_a + kBM - 1) / kBM;
     CUtensorMap map_a, map_b;
-    if (!make_tmap_bf16_2d(&map_a, a_bf, (uint64_t)n_mt * kBM, (uint64_t)C, (uint64_t)C * 2, kBK, kBM) ||
-        !make_tmap_bf16_2d(&map_b, vt, (uint64_t)N_v * P, (uint64_t)C, (uint64_t)C * 2, kBK, kBN)) {
-        set_error("bf16 head: cuTensorMapEncodeTiled failed");
+    if (!make_tmap_f16_2d(&map_a, a_h, (uint64_t)n_mt * kBM, (uint64_t)C, (uint64_t)C * 2, kBK, kBM) ||
+        !make_tmap_f16_2d(&map_b, vt, (uint64_t)N_v * P, (uint64_t)C, (uint64_t)C * 2, kBK, kBN)) {
+        set_error("fp16 head: cuTensorMapEncodeTiled failed");
         return AVT_ERR_CUDA;
     }
     int dev = 0, sms = 148;
@@ -304,38 +309,38 @@ static int launch_sim_tc(bool grad, const __nv_bfloat16* vt, const __nv_bfloat16
     const int grid = groups * mt_par;
     const int L = N_a + 1 + (hp.use_neg ? 1 : 0);
     if (grad) {
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_bf16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)kTcSmemBytes));
-        sim_bf16_kernel<true><<<grid, kTcThreads, kTcSmemBytes, st>>>(
+        sim_tc_kernel<true><<<grid, kTcThreads, kTcSmemBytes, st>>>(
             map_a, map_b, pos_idx, col_offset, N_v, N_a, n_mt, groups, C / kBK, P, hp, L, logits, sim, den,
-            gsim, GA, G, n_a_pad);
+            gsim, GA, G, n_a_pad, gmax_bits);
     } else {
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)kTcSmemBytes));
-        sim_bf16_kernel<false><<<grid, kTcThreads, kTcSmemBytes, st>>>(
+        sim_tc_kernel<false><<<grid, kTcThreads, kTcSmemBytes, st>>>(
             map_a, map_b, pos_idx, col_offset, N_v, N_a, n_mt, groups, C / kBK, P, hp, L, logits, sim, den,
-            nullptr, nullptr, nullptr, 0);
+            nullptr, nullptr, nullptr, 0, nullptr);
     }
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }
 
-int launch_sim_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
+int launch_sim_f16(const __half* vt, const __half* a_h, const int32_t* pos_idx,
                     int col_offset, int N_v, int N_a, int C, int P, HeadParams hp, float* logits,
                     float* sim, float* den, cudaStream_t st) {
     ProfScope _ps(kProfSim, st);
-    return launch_sim_tc(false, vt, a_bf, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den,
-                         nullptr, nullptr, nullptr, 0, st);
+    return launch_sim_tc(false, vt, a_h, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den,
+                         nullptr, nullptr, nullptr, 0, nullptr, st);
 }
 
-// backward stage 1: cell gradients G (bf16, [N_v*P][n_a_pad])
-int launch_grad_cells_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
+// backward stage 1: cell gradients G (fp16, [N_v*P][n_a_pad])
+int launch_grad_cells_f16(const __half* vt, const __half* a_h, const int32_t* pos_idx,
                            int col_offset, int N_v, int N_a, int n_a_pad, int C, int P, HeadParams hp,
                            const float* sim, const float* den, const float* gsim, const float* GA,
-                           __nv_bfloat16* G, cudaStream_t st) {
+                           __half* G, const unsigned int* gmax_bits, cudaStream_t st) {
     ProfScope _ps(kProfBwdG, st);
-    return launch_sim_tc(true, vt, a_bf, pos_idx, col_offset, N_v, N_a, C, P, hp, nullptr,
-                         const_cast<float*>(sim), const_cast<float*>(den), gsim, GA, G, n_a_pad, st);
+    return launch_sim_tc(true, vt, a_h, pos_idx, col_offset, N_v, N_a, C, P, hp, nullptr,
+                         const_cast<float*>(sim), const_cast<float*>(den), gsim, GA, G, n_a_pad, gmax_bits, st);
 }
 
 }  // namespace avt

@@ -1,7 +1,7 @@
-// AVT_PRECISION_BF16 backward on the tensor cores.  Three stages:
+// AVT_PRECISION_F16 backward on the tensor cores.  Three stages:
 //
-//   1. sim_bf16_kernel<true> (avt_head_tc.cu) recomputes S tile by tile and stores the cell
-//      gradients G[n*P + p][k] as bf16 (row pitch n_a_pad).
+//   1. sim_tc_kernel<true> (avt_head_tc.cu) recomputes S tile by tile and stores the cell
+//      gradients G[n*P + p][k] as fp16 (row pitch n_a_pad).
 //   2. bwd_dv_kernel:  dv_hat[np, c] = sum_k G[np, k] a_hat[k, c]   (M = 128 rows of np,
 //      N = C in two halves of <= 256, K = n_a_pad), epilogue = the F.normalize Jacobian
 //      dv = rn (dv_hat - v_hat <v_hat, dv_hat>) (model.py:117) written straight into the
@@ -20,16 +20,16 @@
 namespace avt {
 using namespace tc;
 
-// ------------------------------------------------------------------ a_hat^T (bf16)
-__global__ void transpose_audio_kernel(const __nv_bfloat16* __restrict__ a_bf, int n_a_pad, int C,
-                                       __nv_bfloat16* __restrict__ at_bf) {
-    __shared__ __nv_bfloat16 tile[32][33];
+// ------------------------------------------------------------------ a_hat^T (fp16)
+__global__ void transpose_audio_kernel(const __half* __restrict__ a_h, int n_a_pad, int C,
+                                       __half* __restrict__ at_h) {
+    __shared__ __half tile[32][33];
     const int k0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
     for (int r = threadIdx.y; r < 32; r += blockDim.y)
-        tile[r][threadIdx.x] = a_bf[(size_t)(k0 + r) * C + c0 + threadIdx.x];
+        tile[r][threadIdx.x] = a_h[(size_t)(k0 + r) * C + c0 + threadIdx.x];
     __syncthreads();
     for (int r = threadIdx.y; r < 32; r += blockDim.y)
-        at_bf[(size_t)(c0 + r) * n_a_pad + k0 + threadIdx.x] = tile[threadIdx.x][r];
+        at_h[(size_t)(c0 + r) * n_a_pad + k0 + threadIdx.x] = tile[threadIdx.x][r];
 }
 
 // ------------------------------------------------------------------ stage 2: dv
@@ -42,10 +42,10 @@ constexpr int kDvBBytes = 256 * kDvBK * 2;            // 32768 (one half of C)
 constexpr int kDvStageBytes = kDvABytes + kDvBBytes;
 constexpr size_t kDvSmemBytes = 1024 + (size_t)kDvStages * kDvStageBytes + 256 + 2 * 2 * kDvBM * 4;
 
-__device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
-__device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
-// 16 consecutive bf16 (32 bytes, 32-byte aligned) through the read-only path in one request
-__device__ __forceinline__ void ld_nc_v8(const __nv_bfloat16* p, uint32_t* r) {
+__device__ __forceinline__ float h_lo(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w & 0xffffu))); }
+__device__ __forceinline__ float h_hi(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w >> 16))); }
+// 16 consecutive fp16 (32 bytes, 32-byte aligned) through the read-only path in one request
+__device__ __forceinline__ void ld_nc_v8(const __half* p, uint32_t* r) {
     asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));
@@ -53,9 +53,9 @@ __device__ __forceinline__ void ld_nc_v8(const __nv_bfloat16* p, uint32_t* r) {
 
 __global__ void __launch_bounds__(kDvThreads, 1)
 bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_at,
-              const __nv_bfloat16* __restrict__ vt,
+              const __half* __restrict__ vt,
               const float* __restrict__ rnorm_v, float* __restrict__ dv, int n_rows, int n_tiles,
-              int KC, int C, int P) {
+              int KC, int C, int P, const unsigned int* __restrict__ gmax_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* stages = base;
@@ -105,7 +105,7 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
             int stage = 0; uint32_t phase = 0, it = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
                 for (int h = 0; h < nh; ++h) {
-                    const uint32_t idesc = make_idesc_bf16(kDvBM, h ? hN1 : hN0, 0, 0);
+                    const uint32_t idesc = make_idesc_f16(kDvBM, h ? hN1 : hN0, 0, 0);
                     mbar_wait(&tmem_empty[h], (it & 1u) ^ 1u);
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + (uint32_t)h * 256u;
@@ -118,7 +118,7 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
                         for (int k = 0; k < kDvBK / 16; ++k) {
                             const uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
                             const uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
-                            umma_bf16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                            umma_f16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
                         }
                         umma_commit(&empty_b[stage]);
                         if (++stage == kDvStages) { stage = 0; phase ^= 1; }
@@ -140,7 +140,7 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
             const int n = rowc / P;
             const int p = rowc - n * P;
             const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-            const __nv_bfloat16* vrow = vt + (size_t)rowc * C;
+            const __half* vrow = vt + (size_t)rowc * C;
             // pass 1: t = <v_hat[row, :], dv_hat[row, :]> over this thread's columns
             float t = 0.f;
             for (int h = 0; h < nh; ++h) {
@@ -156,8 +156,8 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
                     tmem_ld_wait();
 #pragma unroll
                     for (int e = 0; e < 16; ++e) {
-                        t = fmaf(bf_lo(x[e]), __uint_as_float(r[2 * e]), t);
-                        t = fmaf(bf_hi(x[e]), __uint_as_float(r[2 * e + 1]), t);
+                        t = fmaf(h_lo(x[e]), __uint_as_float(r[2 * e]), t);
+                        t = fmaf(h_hi(x[e]), __uint_as_float(r[2 * e + 1]), t);
                     }
                 }
             }
@@ -165,9 +165,9 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
             tp[grp * kDvBM + r_in] = t;
             asm volatile("bar.sync 1, 256;" ::: "memory");
             t = tp[r_in] + tp[kDvBM + r_in];
-            // pass 2: dv = rn * (dv_hat - v_hat * t), NCHW fp32.  v_hat comes from the bf16
+            // pass 2: dv = rn * (dv_hat - v_hat * t), NCHW fp32.  v_hat comes from the fp16
             // row this thread just read (L1/L2-resident), not from a second sweep over v.
-            const float rn = rnorm_v[rowc];
+            const float rn = rnorm_v[rowc] * pow2i(-g_scale_exp(__ldg(gmax_bits)));   // undo the scale of G
             const float rt = rn * t;
             for (int h = 0; h < nh; ++h) {
                 const int hN = h ? hN1 : hN0, cw = hN >> 1;
@@ -183,8 +183,8 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
                     if (valid) {
 #pragma unroll
                         for (int e = 0; e < 16; ++e) {
-                            o[(uint32_t)(2 * e) * Pu] = fmaf(-bf_lo(x[e]), rt, rn * __uint_as_float(r[2 * e]));
-                            o[(uint32_t)(2 * e + 1) * Pu] = fmaf(-bf_hi(x[e]), rt, rn * __uint_as_float(r[2 * e + 1]));
+                            o[(uint32_t)(2 * e) * Pu] = fmaf(-h_lo(x[e]), rt, rn * __uint_as_float(r[2 * e]));
+                            o[(uint32_t)(2 * e + 1) * Pu] = fmaf(-h_hi(x[e]), rt, rn * __uint_as_float(r[2 * e + 1]));
                         }
                     }
                 }
@@ -216,8 +216,9 @@ constexpr size_t kDv2SmemBytes = 1024 + (size_t)kDv2Stages * kDv2StageBytes + 25
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kDvThreads, 1)
 bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_at,
-                   const __nv_bfloat16* __restrict__ vt, const float* __restrict__ rnorm_v,
-                   float* __restrict__ dv, int n_rows, int n_tile_pairs, int KC, int C, int P) {
+                   const __half* __restrict__ vt, const float* __restrict__ rnorm_v,
+                   float* __restrict__ dv, int n_rows, int n_tile_pairs, int KC, int C, int P,
+                   const unsigned int* __restrict__ gmax_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* stages = base;
@@ -268,7 +269,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {                    // ---------------- MMA issuer (leader only)
-            const uint32_t idesc = make_idesc_bf16(256, 256, 0, 0);
+            const uint32_t idesc = make_idesc_f16(256, 256, 0, 0);
             int stage = 0; uint32_t phase = 0, it = 0;
             for (int tp = pair0; tp < n_tile_pairs; tp += pair_step, ++it) {
                 for (int h = 0; h < nh; ++h) {
@@ -283,7 +284,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                         for (int k = 0; k < kDvBK / 16; ++k) {
                             const uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
                             const uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
-                            umma2_bf16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                            umma2_f16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc, (uint32_t)((kc | k) != 0));
                         }
                         umma2_commit_mc(&empty_b[stage], 3);
                         if (++stage == kDv2Stages) { stage = 0; phase ^= 1; }
@@ -305,7 +306,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             const int n = rowc / P;
             const int p = rowc - n * P;
             const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-            const __nv_bfloat16* vrow = vt + (size_t)rowc * C;
+            const __half* vrow = vt + (size_t)rowc * C;
             // v_hat row pieces are fetched ahead of their use: the first half before the
             // accumulator is even ready, the second while the first is being reduced, and the
             // second pass starts with the half that is still in registers.
@@ -327,8 +328,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 tmem_ld_wait();
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
-                    t = fmaf(bf_lo(xa[j][e]), __uint_as_float(r[2 * e]), t);
-                    t = fmaf(bf_hi(xa[j][e]), __uint_as_float(r[2 * e + 1]), t);
+                    t = fmaf(h_lo(xa[j][e]), __uint_as_float(r[2 * e]), t);
+                    t = fmaf(h_hi(xa[j][e]), __uint_as_float(r[2 * e + 1]), t);
                 }
             }
             if (nh == 2) {
@@ -341,8 +342,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     tmem_ld_wait();
 #pragma unroll
                     for (int e = 0; e < 16; ++e) {
-                        t = fmaf(bf_lo(xb[j][e]), __uint_as_float(r[2 * e]), t);
-                        t = fmaf(bf_hi(xb[j][e]), __uint_as_float(r[2 * e + 1]), t);
+                        t = fmaf(h_lo(xb[j][e]), __uint_as_float(r[2 * e]), t);
+                        t = fmaf(h_hi(xb[j][e]), __uint_as_float(r[2 * e + 1]), t);
                     }
                 }
             }
@@ -350,7 +351,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             tpart[grp * kDvBM + r_in] = t;
             asm volatile("bar.sync 1, 256;" ::: "memory");
             t = tpart[r_in] + tpart[kDvBM + r_in];
-            const float rn = rnorm_v[rowc];
+            const float rn = rnorm_v[rowc] * pow2i(-g_scale_exp(__ldg(gmax_bits)));   // undo the scale of G
             const float rt = rn * t;
             // pass 2: dv = rn * dv_hat - (rn t) * v_hat, NCHW fp32; each half is released as soon
             // as it has been written so the next tile's MMAs can start on it
@@ -365,8 +366,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     if (valid) {
 #pragma unroll
                         for (int e = 0; e < 16; ++e) {
-                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-bf_lo(xa[j][e]), rt, rn * __uint_as_float(r[2 * e])));
-                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-bf_hi(xa[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
+                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-h_lo(xa[j][e]), rt, rn * __uint_as_float(r[2 * e])));
+                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-h_hi(xa[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
                         }
                     }
                 }
@@ -384,8 +385,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     if (valid) {
 #pragma unroll
                         for (int e = 0; e < 16; ++e) {
-                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-bf_lo(xb[j][e]), rt, rn * __uint_as_float(r[2 * e])));
-                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-bf_hi(xb[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
+                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-h_lo(xb[j][e]), rt, rn * __uint_as_float(r[2 * e])));
+                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-h_hi(xb[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
                         }
                     }
                 }
@@ -420,7 +421,8 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 
 __global__ void __launch_bounds__(kDaThreads, 1)
 bwd_da_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_vt,
-              float* __restrict__ d_ahat, int N_a, int n_mt, int splits, int n_chunks, int C) {
+              float* __restrict__ d_ahat, int N_a, int n_mt, int splits, int n_chunks, int C,
+                   const unsigned int* __restrict__ gmax_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* stages = base;
@@ -481,9 +483,9 @@ bwd_da_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
                     // consecutive 64-element MN blocks are one box apart (LBO)
                     const uint64_t ad = make_smem_desc(a_addr + k * 2048, kDaBoxBytes, 1024);
                     for (int h = 0; h < nh; ++h) {
-                        const uint32_t idesc = make_idesc_bf16(kDaBM, h ? hN1 : hN0, 1, 1);
+                        const uint32_t idesc = make_idesc_f16(kDaBM, h ? hN1 : hN0, 1, 1);
                         const uint64_t bd = make_smem_desc(b_addr + h * 4 * kDaBoxBytes + k * 2048, kDaBoxBytes, 1024);
-                        umma_bf16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc,
+                        umma_f16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc,
                                      (uint32_t)((ch != ch0) || (k != 0)));
                     }
                 }
@@ -498,6 +500,7 @@ bwd_da_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
         mbar_wait(tmem_full, 0);
         tc_fence_after();
         const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+        const float inv = pow2i(-g_scale_exp(__ldg(gmax_bits)));          // undo the scale of G
         for (int c = 0; c < C; c += 32) {
             uint32_t r[32];
             tmem_ld_32x32(lane_addr + (uint32_t)c, r);
@@ -506,8 +509,8 @@ bwd_da_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
                 float* o = d_ahat + (size_t)k * C + c;
 #pragma unroll
                 for (int i = 0; i < 32; i += 4)
-                    red_add_v4(o + i, __uint_as_float(r[i]), __uint_as_float(r[i + 1]),
-                               __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+                    red_add_v4(o + i, inv * __uint_as_float(r[i]), inv * __uint_as_float(r[i + 1]),
+                               inv * __uint_as_float(r[i + 2]), inv * __uint_as_float(r[i + 3]));
             }
         }
     }
@@ -536,7 +539,8 @@ constexpr size_t kDa2SmemBytes = 1024 + (size_t)kDa2Stages * kDa2StageBytes + 25
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kDa2Threads, 1)
 bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_vt,
-                   float* __restrict__ d_ahat, int N_a, int n_mt, int splits, int n_chunks, int C) {
+                   float* __restrict__ d_ahat, int N_a, int n_mt, int splits, int n_chunks, int C,
+                   const unsigned int* __restrict__ gmax_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* stages = base;
@@ -584,7 +588,7 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {                    // ---------------- MMA issuer (leader only)
-            const uint32_t idesc = make_idesc_bf16(256, 256, 1, 1);
+            const uint32_t idesc = make_idesc_f16(256, 256, 1, 1);
             int stage = 0; uint32_t phase = 0;
             for (int ch = ch0; ch < ch1; ++ch) {
                 mbar_wait(&full_b[stage], phase);
@@ -596,7 +600,7 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     const uint64_t ad = make_smem_desc(a_addr + k * 2048, kDa2BlockBytes, 1024);
                     for (int h = 0; h < nh; ++h) {
                         const uint64_t bd = make_smem_desc(b_addr + h * kDa2BHalfBytes + k * 2048, kDa2BlockBytes, 1024);
-                        umma2_bf16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc,
+                        umma2_f16_ss(tmem_base + (uint32_t)h * 256u, ad, bd, idesc,
                                       (uint32_t)((ch != ch0) || (k != 0)));
                     }
                 }
@@ -611,6 +615,7 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
         mbar_wait(tmem_full, 0);
         tc_fence_after();
         const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+        const float inv = pow2i(-g_scale_exp(__ldg(gmax_bits)));          // undo the scale of G
         for (int c = 0; c < C; c += 32) {
             uint32_t r[32];
             tmem_ld_32x32(lane_addr + (uint32_t)c, r);
@@ -619,8 +624,8 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 float* o = d_ahat + (size_t)k * C + c;
 #pragma unroll
                 for (int i = 0; i < 32; i += 4)
-                    red_add_v4(o + i, __uint_as_float(r[i]), __uint_as_float(r[i + 1]),
-                               __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+                    red_add_v4(o + i, inv * __uint_as_float(r[i]), inv * __uint_as_float(r[i + 1]),
+                               inv * __uint_as_float(r[i + 2]), inv * __uint_as_float(r[i + 3]));
             }
         }
     }
@@ -634,46 +639,78 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
 }
 
 // ------------------------------------------------------------------ launch sequence
-int launch_grad_cells_bf16(const __nv_bfloat16* vt, const __nv_bfloat16* a_bf, const int32_t* pos_idx,
+int launch_grad_cells_f16(const __half* vt, const __half* a_h, const int32_t* pos_idx,
                            int col_offset, int N_v, int N_a, int n_a_pad, int C, int P, HeadParams hp,
                            const float* sim, const float* den, const float* gsim, const float* GA,
-                           __nv_bfloat16* G, cudaStream_t st);
+                           __half* G, const unsigned int* gmax_bits, cudaStream_t st);
 
 // The dv and d_ahat contractions both consume G and are independent of each other: d_ahat is
 // enqueued on a side stream so that its CTAs fill the SMs the dv kernel's last wave leaves idle
 // (matters for small shards: at 128 rows per rank the two kernels are ~1.3 waves each).  Plain
 // event fork / join, so it is captured into CUDA graphs like any cross-stream dependency.
+//
+// One side context PER (device, caller stream): two host threads that drive the same device on
+// their own streams (the nn.DataParallel caller of SURVEY 8b) never share an event, so one
+// caller's record can not be consumed by the other's wait.  The table only grows with the number
+// of distinct caller streams (bounded; past the bound the d_ahat kernel simply stays on the
+// caller's stream) and the mutex guards the lookup alone.
 struct SideStream {
+    int dev = -1;
+    cudaStream_t owner = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t fork = nullptr, join = nullptr, fork0 = nullptr, tdone = nullptr;
 };
-static SideStream* side_stream(int dev) {
+constexpr int kMaxSideCtx = 128;
+static SideStream* side_stream(int dev, cudaStream_t owner) {
     static std::mutex mu;
-    static SideStream ctx[64];
-    if (dev < 0 || dev >= 64) return nullptr;
+    static SideStream ctx[kMaxSideCtx];
+    static int used = 0;
     std::lock_guard<std::mutex> lock(mu);
-    SideStream& c = ctx[dev];
-    if (!c.stream) {
-        if (cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming) != cudaSuccess ||
-            cudaEventCreateWithFlags(&c.join, cudaEventDisableTiming) != cudaSuccess ||
-            cudaEventCreateWithFlags(&c.fork0, cudaEventDisableTiming) != cudaSuccess ||
-            cudaEventCreateWithFlags(&c.tdone, cudaEventDisableTiming) != cudaSuccess) {
-            c.stream = nullptr;
-            (void)cudaGetLastError();
-            return nullptr;
-        }
-    }
-    return &c;
+    for (int i = 0; i < used; ++i)
+        if (ctx[i].dev == dev && ctx[i].owner == owner) return &ctx[i];
+    if (used == kMaxSideCtx) return nullptr;
+    // creating a stream / events is illegal while `owner` is capturing only for the legacy
+    // stream; ours are non-blocking streams and plain events, allowed under relaxed capture
+    cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+    cudaThreadExchangeStreamCaptureMode(&mode);
+    SideStream c;
+    c.dev = dev; c.owner = owner;
+    const bool ok = cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking) == cudaSuccess &&
+                    cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming) == cudaSuccess &&
+                    cudaEventCreateWithFlags(&c.join, cudaEventDisableTiming) == cudaSuccess &&
+                    cudaEventCreateWithFlags(&c.fork0, cudaEventDisableTiming) == cudaSuccess &&
+                    cudaEventCreateWithFlags(&c.tdone, cudaEventDisableTiming) == cudaSuccess;
+    cudaThreadExchangeStreamCaptureMode(&mode);
+    if (!ok) { (void)cudaGetLastError(); return nullptr; }
+    ctx[used] = c;
+    return &ctx[used++];
 }
 
-int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16* a_bf,
-                    __nv_bfloat16* at_bf, __nv_bfloat16* g_bf, const float* a_hat, const float* rnorm_v,
+// AVT_NO_SIDE_STREAM / AVT_NO_PAIR are development switches: read ONCE per process
+struct EnvSwitches { bool no_side, no_pair; };
+static const EnvSwitches& env_switches() {
+    static const EnvSwitches e{getenv("AVT_NO_SIDE_STREAM") != nullptr, getenv("AVT_NO_PAIR") != nullptr};
+    return e;
+}
+
+// joins the side stream back into the caller's stream on EVERY exit path once it has forked, so an
+// error return can not leave a capturing stream with an unjoined branch
+struct SideJoin {
+    SideStream* side; cudaStream_t st; bool forked = false;
+    ~SideJoin() {
+        if (!side || !forked) return;
+        if (cudaEventRecord(side->join, side->stream) == cudaSuccess) cudaStreamWaitEvent(st, side->join, 0);
+    }
+};
+
+int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
+                    __half* at_h, __half* g_h, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C, int P,
                     HeadParams hp, const float* sim, const float* den, const float* gsim,
-                    const float* GA, float* dv, float* d_ahat, cudaStream_t st) {
+                    const float* GA, float* dv, float* d_ahat, const unsigned int* gmax_bits,
+                    cudaStream_t st) {
     (void)a_hat; (void)v;
-    AVT_REQUIRE(C % 64 == 0 && C <= 512, "bf16 backward: C=%d must be a multiple of 64, <= 512", C);
+    AVT_REQUIRE(C % 64 == 0 && C <= 512, "fp16 backward: C=%d must be a multiple of 64, <= 512", C);
     const int n_rows = N_v * P;
     int dev = 0, sms = 148;
     AVT_CHECK_CUDA(cudaGetDevice(&dev));
@@ -681,21 +718,24 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
 
     // the side stream first transposes the audio operand of stage 2 while stage 1 runs, then (after
     // stage 1) carries stage 3 concurrently with stage 2
-    SideStream* side = getenv("AVT_NO_SIDE_STREAM") ? nullptr : side_stream(dev);
+    const EnvSwitches& env = env_switches();
+    SideStream* side = env.no_side ? nullptr : side_stream(dev, st);
     cudaStream_t st_da = side ? side->stream : st;
+    SideJoin joiner{side, st};
     if (side) {
         AVT_CHECK_CUDA(cudaEventRecord(side->fork0, st));
         AVT_CHECK_CUDA(cudaStreamWaitEvent(side->stream, side->fork0, 0));
+        joiner.forked = true;
     }
     {
         dim3 grid(n_a_pad / 32, C / 32), block(32, 8);
-        transpose_audio_kernel<<<grid, block, 0, st_da>>>(a_bf, n_a_pad, C, at_bf);
+        transpose_audio_kernel<<<grid, block, 0, st_da>>>(a_h, n_a_pad, C, at_h);
         AVT_LAUNCH_CHECK();
     }
     if (side) AVT_CHECK_CUDA(cudaEventRecord(side->tdone, side->stream));
     // stage 1: cell gradients
-    int rc = launch_grad_cells_bf16(vt, a_bf, pos_idx, col_offset, N_v, N_a, n_a_pad, C, P, hp, sim, den,
-                                    gsim, GA, g_bf, st);
+    int rc = launch_grad_cells_f16(vt, a_h, pos_idx, col_offset, N_v, N_a, n_a_pad, C, P, hp, sim, den,
+                                    gsim, GA, g_h, gmax_bits, st);
     if (rc != AVT_OK) return rc;
     if (side) {
         AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->tdone, 0));
@@ -705,11 +745,11 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
     // stage 2: dv
     {
         ProfScope _ps(kProfBwdDv, st);
-        const bool pair = (C == 256 || C == 512) && !getenv("AVT_NO_PAIR");
+        const bool pair = (C == 256 || C == 512) && !env.no_pair;
         CUtensorMap map_g, map_at;
-        if (!make_tmap_bf16_2d(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, kDvBM) ||
-            !make_tmap_bf16_2d(&map_at, at_bf, (uint64_t)C, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, pair ? 128 : 256)) {
-            set_error("bf16 backward: cuTensorMapEncodeTiled failed (dv)");
+        if (!make_tmap_f16_2d(&map_g, g_h, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, kDvBM) ||
+            !make_tmap_f16_2d(&map_at, at_h, (uint64_t)C, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, pair ? 128 : 256)) {
+            set_error("fp16 backward: cuTensorMapEncodeTiled failed (dv)");
             return AVT_ERR_CUDA;
         }
         const int n_tiles = (n_rows + kDvBM - 1) / kDvBM;
@@ -719,13 +759,13 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDv2SmemBytes));
             bwd_dv_pair_kernel<<<2 * grid_pairs, kDvThreads, kDv2SmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv,
-                                                                                  n_rows, n_pairs, n_a_pad / kDvBK, C, P);
+                                                                                  n_rows, n_pairs, n_a_pad / kDvBK, C, P, gmax_bits);
         } else {
             const int grid = n_tiles < sms ? n_tiles : sms;
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDvSmemBytes));
             bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv, n_rows,
-                                                                 n_tiles, n_a_pad / kDvBK, C, P);
+                                                                 n_tiles, n_a_pad / kDvBK, C, P, gmax_bits);
         }
         AVT_LAUNCH_CHECK();
     }
@@ -733,18 +773,18 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
     {
         ProfScope _ps(kProfBwdDa, st_da);
         const int n_mt = n_a_pad / kDaBM;
-        const bool pair = (n_mt % 2 == 0) && (C == 256 || C == 512) && !getenv("AVT_NO_PAIR");
+        const bool pair = (n_mt % 2 == 0) && (C == 256 || C == 512) && !env.no_pair;
         const int bk = pair ? kDa2BK : kDaBK;
         CUtensorMap map_g, map_vt;
         bool ok;
         if (pair)
-            ok = make_tmap_bf16_blocks(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, bk, 2) &&
-                 make_tmap_bf16_blocks(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, bk, 2);
+            ok = make_tmap_f16_blocks(&map_g, g_h, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, bk, 2) &&
+                 make_tmap_f16_blocks(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, bk, 2);
         else
-            ok = make_tmap_bf16_2d(&map_g, g_bf, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, 64, bk) &&
-                 make_tmap_bf16_2d(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, 64, bk);
+            ok = make_tmap_f16_2d(&map_g, g_h, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, 64, bk) &&
+                 make_tmap_f16_2d(&map_vt, vt, (uint64_t)n_rows, (uint64_t)C, (uint64_t)C * 2, 64, bk);
         if (!ok) {
-            set_error("bf16 backward: cuTensorMapEncodeTiled failed (d_ahat)");
+            set_error("fp16 backward: cuTensorMapEncodeTiled failed (d_ahat)");
             return AVT_ERR_CUDA;
         }
         const int n_chunks = (n_rows + bk - 1) / bk;
@@ -756,20 +796,16 @@ int launch_bwd_bf16(const float* v, const __nv_bfloat16* vt, const __nv_bfloat16
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDa2SmemBytes));
             bwd_da_pair_kernel<<<n_mt * splits, kDa2Threads, kDa2SmemBytes, st_da>>>(map_g, map_vt, d_ahat, N_a,
-                                                                                  n_mt, splits, n_chunks, C);
+                                                                                  n_mt, splits, n_chunks, C, gmax_bits);
         } else {
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDaSmemBytes));
             bwd_da_kernel<<<n_mt * splits, kDaThreads, kDaSmemBytes, st_da>>>(map_g, map_vt, d_ahat, N_a, n_mt,
-                                                                          splits, n_chunks, C);
+                                                                          splits, n_chunks, C, gmax_bits);
         }
         AVT_LAUNCH_CHECK();
     }
-    if (side) {                                      // join
-        AVT_CHECK_CUDA(cudaEventRecord(side->join, side->stream));
-        AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->join, 0));
-    }
-    return AVT_OK;
+    return AVT_OK;                                   // `joiner` joins the side stream
 }
 
 }  // namespace avt

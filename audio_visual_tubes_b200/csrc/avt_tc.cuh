@@ -109,8 +109,8 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-// D[tmem] (+)= A[smem] * B[smem], bf16 inputs, fp32 accumulate; issued by ONE thread
-__device__ __forceinline__ void umma_bf16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+// D[tmem] (+)= A[smem] * B[smem], fp16 inputs, fp32 accumulate; issued by ONE thread
+__device__ __forceinline__ void umma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
                                              uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -120,7 +120,7 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t d_tmem, uint64_t a_desc, u
         : "memory");
 }
 // D[tmem] (+)= A[tmem] * B[smem]
-__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
+__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
                                              uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -198,7 +198,7 @@ __device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
 // D[tmem, both CTAs] (+)= A * B with M = 256; issued by ONE thread of the leader CTA
-__device__ __forceinline__ void umma2_bf16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+__device__ __forceinline__ void umma2_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
                                               uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -254,11 +254,12 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
     d |= (uint64_t)2 << 61;
     return d;
 }
-// Instruction descriptor for kind::f16 with bf16 operands and fp32 accumulate
-// (cute::UMMA::InstrDescriptor): c_format F32 = 1 @4, a/b_format BF16 = 1 @7/@10,
+// Instruction descriptor for kind::f16 with fp16 operands and fp32 accumulate
+// (cute::UMMA::InstrDescriptor): c_format F32 = 1 @4, a/b_format @7/@10 (F16 = 0, BF16 = 1:
+// IEEE half operands, 11-bit significand -- see DESIGN.md section 2 for why not bf16),
 // a_major @15, b_major @16 (0 = K-major, 1 = MN-major), N >> 3 @17, M >> 4 @24.
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) |
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, int a_mn_major, int b_mn_major) {
+    return (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)a_mn_major << 15) |
            ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
@@ -280,8 +281,8 @@ inline EncodeTiledFn get_encode_tiled() {
     return fn;
 }
 
-// row-major 2-D bf16 tensor [rows][cols], box {box_cols, box_rows}, 128-byte swizzle
-inline bool make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+// row-major 2-D fp16 tensor [rows][cols], box {box_cols, box_rows}, 128-byte swizzle
+inline bool make_tmap_f16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                               uint64_t row_pitch_bytes, uint32_t box_cols, uint32_t box_rows) {
     EncodeTiledFn enc = get_encode_tiled();
     if (!enc) return false;
@@ -289,17 +290,17 @@ inline bool make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows,
     cuuint64_t strides[1] = {row_pitch_bytes};
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box,
                      estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }
 
 
-// row-major 2-D bf16 tensor [rows][cols] viewed as 3-D {64 columns, rows, column blocks of 64}:
+// row-major 2-D fp16 tensor [rows][cols] viewed as 3-D {64 columns, rows, column blocks of 64}:
 // one box {64, box_rows, box_blocks} lands as box_blocks consecutive [box_rows][128 B] tiles --
 // the MN-major SW128 operand layout (blocks one LBO apart), with a single TMA instruction.
-inline bool make_tmap_bf16_blocks(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+inline bool make_tmap_f16_blocks(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                                   uint64_t row_pitch_bytes, uint32_t box_rows, uint32_t box_blocks) {
     EncodeTiledFn enc = get_encode_tiled();
     if (!enc) return false;
@@ -307,7 +308,7 @@ inline bool make_tmap_bf16_blocks(CUtensorMap* out, const void* base, uint64_t r
     cuuint64_t strides[2] = {row_pitch_bytes, 128};
     cuuint32_t box[3] = {64, box_rows, box_blocks};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box,
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box,
                      estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;

@@ -169,11 +169,12 @@ def eval_maps_raw(maps14, gt_dense=None, boxes=None, box_count=None, gt_mode="vg
     union = torch.empty(n, dtype=torch.int32, device=dev)
     ciou = torch.empty(n, dtype=torch.float64, device=dev)
     mb = 0 if boxes is None else boxes.shape[1]
+    ws = torch.empty(_lib.EVAL_WORKSPACE_BYTES, dtype=torch.uint8, device=dev)   # this call's ticket word
     with torch.cuda.device(dev):
         _lib.check(lib.avt_eval_maps(_lib.ptr(maps14), n, _lib.ptr(gt_dense), _lib.ptr(boxes),
                                      _lib.ptr(box_count), mb, GT_MODES[gt_mode], _lib.ptr(up),
                                      _lib.ptr(mk), _lib.ptr(inter), _lib.ptr(union), _lib.ptr(ciou),
-                                     _lib.stream_ptr()), "avt_eval_maps")
+                                     _lib.ptr(ws), _lib.stream_ptr()), "avt_eval_maps")
     return dict(up224=up, mask=mk, inter_w=inter, union_w=union, ciou=ciou)
 
 

@@ -17,7 +17,7 @@ import torch
 
 from . import _lib
 
-PRECISION = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}
+PRECISION = {"fp32": _lib.PRECISION_FP32, "f16": _lib.PRECISION_F16}
 
 
 @dataclass(frozen=True)
@@ -32,7 +32,7 @@ class HeadConfig:
     mask_scale: float = 100.0
     trimap: bool = True
     use_neg: bool = True
-    precision: str = "bf16"
+    precision: str = "f16"
 
 
 def audio_normalize(a: torch.Tensor):
@@ -100,7 +100,7 @@ def head_forward_raw(v, a_hat, cfg: HeadConfig, pos_idx=None, col_offset=0, want
 
 
 def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits=None, dA=None,
-                      col_offset=0, dW=None):
+                      col_offset=0, dW=None, dloss_rows=None):
     """One ``avt_head_backward`` call.  Returns (dv [N_v,C,P], d_ahat [N_a,C])."""
     lib = _lib.load()
     n_v, c, p = v.shape
@@ -118,6 +118,8 @@ def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits
         dA = dA.contiguous().float().view(n_v, p)
     if dW is not None:
         dW = dW.contiguous().float().view(n_v, p)
+    if dloss_rows is not None:
+        dloss_rows = dloss_rows.contiguous().float().view(n_v)
     with torch.cuda.device(v.device):
         rc = lib.avt_head_backward(
             _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(saved["pos_idx"]), int(col_offset),
@@ -125,7 +127,7 @@ def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits
             prec, int(saved.get("col_mult", 1)), _lib.ptr(saved["A"]), _lib.ptr(saved["logits"]),
             _lib.ptr(saved["loss_rows"]),
             _lib.ptr(saved["rnorm_v"]), _lib.ptr(saved["sim"]), _lib.ptr(saved["den"]),
-            float(dloss_scale), _lib.ptr(dlogits), _lib.ptr(dA), _lib.ptr(dW), _lib.ptr(dv),
+            float(dloss_scale), _lib.ptr(dloss_rows), _lib.ptr(dlogits), _lib.ptr(dA), _lib.ptr(dW), _lib.ptr(dv),
             _lib.ptr(d_ahat),
             _lib.ptr(ws), C.c_size_t(ws.numel()), _lib.stream_ptr())
     _lib.check(rc, "avt_head_backward")
@@ -196,27 +198,19 @@ class _HardWayHead(torch.autograd.Function):
         else:
             ctx.mark_non_differentiable(out["Pos"], out["Neg"], w)
         logits = out["logits"] if col_mult == 1 else expand_tube_logits(out, cfg, copy_idx)
-        ctx.logits_full = logits
         return out["A"], logits, out["Pos"], out["Neg"], w, out["loss_rows"]
 
     @staticmethod
     def backward(ctx, gA, glogits, gPos, gNeg, gW, gloss_rows):
         v, a_hat, rn_a = ctx.saved_tensors
         dlogits = glogits
-        # d loss_rows[n] / d logits[n, :] = softmax - onehot(0); fold a row-wise upstream
-        # gradient into dlogits unless it is one uniform scalar (the mean / sum case)
-        scale = 0.0
-        if gloss_rows is not None:
-            g = gloss_rows.contiguous().float()
-            lg = ctx.logits_full
-            sm = torch.softmax(lg, dim=1)
-            sm[:, 0] -= 1.0
-            extra = sm * g[:, None]
-            dlogits = extra if dlogits is None else dlogits + extra
+        # d loss_rows[n] / d logits[n, :] = softmax - onehot(0) is formed inside row_grad_kernel from
+        # the per-row upstream gradient (dloss_rows): no eager softmax on the host side
         if dlogits is not None and ctx.saved["col_mult"] > 1:
             dlogits = reduce_tube_dlogits(dlogits.contiguous().float(), ctx.saved, ctx.cfg, ctx.copy_idx)
-        dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, scale, dlogits, gA,
-                                       ctx.col_offset, gW if ctx.want_weighted else None)
+        dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, 0.0, dlogits, gA,
+                                       ctx.col_offset, gW if ctx.want_weighted else None,
+                                       dloss_rows=gloss_rows)
         da = audio_normalize_backward(a_hat, rn_a, d_ahat)
         return dv, da, None, None, None, None, None, None
 

@@ -20,7 +20,7 @@ from .head import HeadConfig, audio_normalize, hardway_head, hardway_loss
 
 
 class AVENet(nn.Module):
-    def __init__(self, args, pretrained=False, precision: str = "bf16", return_weighted: bool = False):
+    def __init__(self, args, pretrained=False, precision: str = "f16", return_weighted: bool = False):
         super().__init__()
         self.imgnet = resnet18_2d("vision")
         self.audnet = resnet18_2d("audio")
@@ -78,7 +78,7 @@ class HardWayAttention(nn.Module):
     ``[(bT), (bT)+2]`` -- at 1/T of the similarity flops (and run the audio backbone on b
     spectrograms instead of bT)."""
 
-    def __init__(self, precision: str = "bf16"):
+    def __init__(self, precision: str = "f16"):
         super().__init__()
         self.epsilon, self.epsilon2, self.tau = 0.65, 0.4, 0.03
         self.precision = precision
@@ -97,7 +97,7 @@ class HardWayAttention(nn.Module):
 
 
 class FullModel(nn.Module):
-    def __init__(self, args=None, precision: str = "bf16"):
+    def __init__(self, args=None, precision: str = "f16"):
         super().__init__()
         self.vidnet = resnet18_3d(n_classes=1039)
         self.audnet = resnet18_2d("audio")

@@ -37,7 +37,9 @@ extern "C" {
 
 /* precision of the all-pairs contraction (model.py:125) */
 #define AVT_PRECISION_FP32     0   /* CUDA-core fp32 FMA, the reference's own arithmetic */
-#define AVT_PRECISION_BF16     1   /* tcgen05 kind::f16 (bf16 operands, fp32 accumulate in TMEM) */
+#define AVT_PRECISION_F16      1   /* tcgen05 kind::f16: IEEE fp16 operands (11-bit significand; the
+                                      operands are L2-normalised, the cell gradients carry a
+                                      power-of-two scale), fp32 accumulate in tensor memory */
 
 /* ground-truth rasterisation modes (utils.py:241-309) */
 #define AVT_GT_VGGSS           0   /* union of boxes            -> weights {0,1},   den 1 */
@@ -120,9 +122,9 @@ int avt_head_forward(const float* v, const float* a_hat,
                      void* workspace, size_t workspace_bytes, void* stream);
 
 /* Backward of the head (autograd of model.py:117-146 + CrossEntropyLoss).
- * Gradient of   dloss_scale * sum_n loss_rows[n]  +  <dlogits, logits>  +  <dA, A>
- *               +  <dWeighted, weighted_A>
- * (dlogits, dA, dWeighted [N_v, P] may be NULL; dWeighted is what train_hardway.py:138-142
+ * Gradient of   dloss_scale * sum_n loss_rows[n]  +  <dloss_rows, loss_rows>  +  <dlogits, logits>
+ *               +  <dA, A>  +  <dWeighted, weighted_A>
+ * (dloss_rows [N_v], dlogits, dA, dWeighted [N_v, P] may be NULL; dWeighted is what train_hardway.py:138-142
  * sends back through weighted_A = mean_c(v_hat * normalize(Pos)), model.py:148-152: it
  * reaches v through every channel alike and through Pos -> A; needs the workspace the forward
  * ran with, which still holds mean_c v_hat).  Writes dv [N_v, C, P] (gradient wrt the RAW maps) and
@@ -136,7 +138,8 @@ int avt_head_backward(const float* v, const float* a_hat,
                       int trimap, int use_neg, int precision, int col_mult,
                       const float* A, const float* logits, const float* loss_rows,
                       const float* rnorm_v, const float* sim, const float* den,
-                      float dloss_scale, const float* dlogits, const float* dA,
+                      float dloss_scale, const float* dloss_rows,
+                      const float* dlogits, const float* dA,
                       const float* dWeighted,
                       float* dv, float* d_ahat,
                       void* workspace, size_t workspace_bytes, void* stream);
@@ -156,12 +159,17 @@ int avt_head_backward(const float* v, const float* a_hat,
  *   mask       [N, 224, 224] uint8 or NULL    the binary prediction (:203-204)
  *   inter_w, union_w [N] int32    integer numerator / denominator in weight units:
  *              ciou = inter_w / union_w exactly as utils.py:212-214 computes in float64
- *   ciou       [N] float64        (NaN when union_w == 0, as numpy)            */
+ *   ciou       [N] float64        (NaN when union_w == 0, as numpy)
+ *   workspace  AVT_EVAL_WORKSPACE_BYTES device bytes owned by this call until it completes (the
+ *              work-ticket word; zeroed by the library on `stream`), so concurrent launches,
+ *              captured graphs and failed launches share no state                        */
+#define AVT_EVAL_WORKSPACE_BYTES 64
 int avt_eval_maps(const float* maps14, int N,
                   const uint8_t* gt_dense,
                   const int16_t* boxes, const uint8_t* box_count, int max_boxes, int gt_mode,
                   float* up224, uint8_t* mask,
-                  int32_t* inter_w, int32_t* union_w, double* ciou, void* stream);
+                  int32_t* inter_w, int32_t* union_w, double* ciou,
+                  void* workspace, void* stream);
 
 /* Selection statistics of avt_eval_maps since the last reset (host array of 2):
  *   out2[0] = maps whose median-rank threshold (train_hardway_1frame.py:202, np.sort(...)[25088])

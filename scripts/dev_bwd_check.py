@@ -23,6 +23,6 @@ def rn(a, b):
 for n_v, n_a in [(8, 8), (3, 5), (33, 17), (7, 130), (128, 128), (64, 1024)]:
     for mode in ("mix", "relu"):
         l0, dv0, da0 = run(n_v, n_a, "fp32", mode)
-        l1, dv1, da1 = run(n_v, n_a, "bf16", mode)
+        l1, dv1, da1 = run(n_v, n_a, "f16", mode)
         print(f"N_v={n_v} N_a={n_a} {mode}: loss {l0:.6f}/{l1:.6f}  dv rel {rn(dv1, dv0):.2e}  da rel {rn(da1, da0):.2e}"
               f"  |dv| {np.linalg.norm(dv0):.3e} |da| {np.linalg.norm(da0):.3e}", flush=True)

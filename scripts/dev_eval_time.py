@@ -18,6 +18,7 @@ gt = torch.zeros(n, 224, 224, dtype=torch.uint8, device=dev); gt[:, 40:160, 50:1
 up = torch.empty(n, 224, 224, device=dev); mk = torch.empty(n, 224, 224, dtype=torch.uint8, device=dev)
 iw = torch.empty(n, dtype=torch.int32, device=dev); uw = torch.empty_like(iw)
 ci = torch.empty(n, dtype=torch.float64, device=dev)
+tk = torch.empty(64, dtype=torch.uint8, device=dev)
 bx = torch.tensor([[[50, 40, 180, 160]]], dtype=torch.int16, device=dev).repeat(n, 1, 1).contiguous()
 bc = torch.ones(n, dtype=torch.uint8, device=dev)
 lib = _lib.load()
@@ -28,7 +29,7 @@ def run(mode):
     else:
         a = (_lib.ptr(maps), n, _lib.ptr(gt), None, None, 0, 0,
              _lib.ptr(up) if mode == "mat" else None, _lib.ptr(mk) if mode == "mat" else None)
-    _lib.check(lib.avt_eval_maps(*a, _lib.ptr(iw), _lib.ptr(uw), _lib.ptr(ci), _lib.stream_ptr()), "avt_eval_maps")
+    _lib.check(lib.avt_eval_maps(*a, _lib.ptr(iw), _lib.ptr(uw), _lib.ptr(ci), _lib.ptr(tk), _lib.stream_ptr()), "avt_eval_maps")
 
 import ctypes
 st = (ctypes.c_ulonglong * 2)()

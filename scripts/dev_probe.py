@@ -32,7 +32,7 @@ def main():
         ms = timeit(lambda: ev.eval_maps_raw(maps, gt_dense=gt))
         print(f"eval dense-gt, scalars only: {ms:.3f} ms  {n/ms*1e3:.0f} maps/s")
     if "head" in what:
-        for prec in ("fp32", "bf16"):
+        for prec in ("fp32", "f16"):
             for B in (128, 1024):
                 if prec == "fp32" and B == 1024:
                     continue

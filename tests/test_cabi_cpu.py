@@ -42,8 +42,8 @@ def test_version_and_error_paths_without_gpu(lib):
     assert rc == -1 and b"N_v" in lib.avt_last_error()
     assert lib.avt_head_workspace_bytes(128, 128, 512, 196, 1, 1) > 128 * 196 * 512 * 2
     assert lib.avt_head_workspace_bytes(128, 128, 512, 196, 0, 0) < 1 << 20
-    assert lib.avt_eval_maps(None, 0, None, None, None, 0, 0, None, None, None, None, None, None) == 0
-    assert lib.avt_eval_maps(None, 4, None, None, None, 0, 0, None, None, None, None, None, None) == -1
+    assert lib.avt_eval_maps(None, 0, None, None, None, 0, 0, None, None, None, None, None, None, None) == 0
+    assert lib.avt_eval_maps(None, 4, None, None, None, 0, 0, None, None, None, None, None, None, None) == -1
 
 
 def test_product_path_refuses_cpu_tensors():

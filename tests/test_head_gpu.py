@@ -1,8 +1,9 @@
 """GPU parity of the similarity + hard-way loss head: libavtubes (through the C ABI) against
 the golden vectors of the unmodified reference and against the CPU oracle.
 
-Tolerances (BASELINE.json north_star): logits / loss / maps within 2e-3 relative for the
-bf16 tensor-core path; the fp32 path is held to fp32 round-off."""
+Tolerances (BASELINE.json north_star): logits / loss / maps within 2e-3 relative and
+gradients within 2e-3 norm-wise for the tensor-core path (fp16 operands, fp32 accumulate); the
+fp32 CUDA-core path is held to fp32 round-off."""
 import os
 
 import numpy as np
@@ -18,13 +19,14 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden")
 HEAD = np.load(os.path.join(GOLD, "head_golden.npz"))
 HEAD_CASES = [("cfg1_relu", "relu"), ("cfg1_mix", "mix"), ("b32_mix", "mix"),
               ("b16_notrimap", "mix"), ("b16_noneg", "mix"), ("b8_signed", "signed")]
-# (max-norm relative tolerance of logits / maps, norm-wise gradient tolerance).  north_star
-# states 2e-3 for logits / loss / maps on the bf16 tensor-core path.  Gradients of the bf16
-# path are the exact gradients of the bf16-rounded forward: the softmax over logits/0.07
-# amplifies the forward's 2e-4 logit error ~14x, and d_ahat sums strongly cancelling terms
-# over all rows, so its norm-wise error against the fp64 autograd oracle is held to 1e-2.
-TOL = {"fp32": (2e-5, 2e-4), "bf16": (2e-3, 1e-2)}
-PRECISIONS = ["fp32", "bf16"]
+# (max-norm relative tolerance of logits / maps, norm-wise gradient tolerance).  SURVEY 8c states
+# 2e-3 for both on the tensor-core path.  Round 1 ran bf16 operands and could only hold gradients
+# to 1e-2: a row's gradient is dominated by ONE term (the -99-weighted diagonal column), so the
+# 2^-9 rounding of each bf16 factor (a_hat, G, v_hat) shows up un-averaged (measured 3e-3..6e-3;
+# scripts/sim_bf16_grad_error.py attributes it).  fp16 operands (2^-11, same tensor-core rate) with a
+# power-of-two scale on the cell gradients measure 4e-4..8e-4 and meet the stated 2e-3.
+TOL = {"fp32": (2e-5, 2e-4), "f16": (2e-3, 2e-3)}
+PRECISIONS = ["fp32", "f16"]
 
 
 def rel(a, b):
@@ -317,7 +319,7 @@ def test_weighted_map_gradient_vs_oracle(n, mode, precision):
         total.backward()
         assert rel(wA.detach().cpu().numpy(), o["weighted_A"]) < TOL[precision][0]
         # the channel-uniform part of dv is exact fp32 in both precisions; the part through
-        # Pos -> A rides the bf16 contraction like every other map gradient
+        # Pos -> A rides the fp16 contraction like every other map gradient
         assert relnorm(vt.grad.cpu().numpy(), dv) < TOL[precision][1], (scale, relnorm(vt.grad.cpu().numpy(), dv))
         assert relnorm(at.grad.cpu().numpy(), da) < TOL[precision][1], (scale, relnorm(at.grad.cpu().numpy(), da))
 
@@ -387,3 +389,136 @@ def test_avenet_contract():
     loss = net.loss(img, aud)
     loss.backward()
     assert torch.isfinite(loss) and net.imgnet.conv1.weight.grad is not None
+
+
+# ---------------------------------------------------------------------------------------------
+# The shapes bench.py measures ("the benchmarked shape has no backward parity").
+def _run_value_and_grad(v, a, precision, **kw):
+    from audio_visual_tubes_b200 import HeadConfig, hardway_value_and_grad
+    vt = torch.tensor(v, device="cuda"); at = torch.tensor(a, device="cuda")
+    loss, dv, da = hardway_value_and_grad(vt, at, HeadConfig(precision=precision), **kw)
+    torch.cuda.synchronize()
+    return float(loss[0]), dv.cpu().numpy(), da.cpu().numpy()
+
+
+@pytest.fixture(scope="module")
+def cfg5_case():
+    """Config 5 at full size, N_v = N_a = 1024, bench.py's |randn| features; fp64 autograd oracle in
+    row blocks (rows are independent given all audio columns; da accumulates across blocks)."""
+    rng = np.random.default_rng(1234)
+    v = np.abs(rng.standard_normal((1024, 512, 196), dtype=np.float32))
+    a = np.abs(rng.standard_normal((1024, 512), dtype=np.float32))
+    o, dv, da = ho.head_forward_backward_blocks(v, a, row_block=64)
+    return v, a, o, dv, da
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_cfg5_b1024_forward_backward(cfg5_case, precision):
+    """n_a_pad = 1024: eight audio tiles (a_full / a_empty reloads), cta_group::2 d_ahat kernel with
+    18 K splits, dv contraction with K = 1024 -- the kernels of the headline bench, against the
+    fp64 oracle: logits / loss / A at 2e-3, gradients at 2e-3 norm-wise."""
+    v, a, o, dv, da = cfg5_case
+    from audio_visual_tubes_b200 import HeadConfig
+    from audio_visual_tubes_b200.head import audio_normalize, head_forward_raw
+    cfg = HeadConfig(precision=precision)
+    tol, gtol = TOL[precision]
+    vt = torch.tensor(v, device="cuda"); at = torch.tensor(a, device="cuda")
+    out = head_forward_raw(vt, audio_normalize(at)[0], cfg)
+    assert rel(out["logits"].cpu().numpy(), o["logits"]) < tol
+    assert rel(out["A"].cpu().numpy(), o["A"]) < tol
+    assert rel(out["loss_rows"].cpu().numpy(), o["loss_rows"]) < 5 * tol
+    loss, dv_g, da_g = _run_value_and_grad(v, a, precision)
+    assert abs(loss - o["loss"]) < tol * max(1.0, abs(o["loss"]))
+    e_dv, e_da = relnorm(dv_g, dv), relnorm(da_g, da)
+    print(f"cfg5 B=1024 [{precision}] loss {loss:.6f} vs {o['loss']:.6f}; norm-wise grad err dv {e_dv:.2e} da {e_da:.2e}")
+    assert e_dv < gtol and e_da < gtol
+    # per-row gradient norms too (a wrong tile / split shows up in SOME rows, not in the norm)
+    rn = np.sqrt((dv_g.astype(np.float64) ** 2).sum((1, 2))); rn_o = np.sqrt((dv ** 2).sum((1, 2)))
+    assert np.abs(rn - rn_o).max() / rn_o.max() < gtol
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_cfg4_tube_64x16_both_modes(precision):
+    """Config 4: b = 64 clips x T = 16 frames = 1024 frames.  Reference-faithful mode (every
+    spectrogram repeated 16 times, train_3D.py:129-130: 1024 audio rows, 15 unmasked duplicate
+    columns per frame) and the de-duplicated tube mode (64 distinct rows, col_mult = 16) against the
+    same fp64 oracle of the repeated problem, forward and backward."""
+    b, t = 64, 16
+    v, a = head_features(b * t, b, 77, "mix")
+    a_rep = np.repeat(a, t, axis=0)
+    o, dv, da_rep = ho.head_forward_backward_blocks(v, a_rep, row_block=64)
+    da = da_rep.reshape(b, t, -1).sum(1)
+    tol, gtol = TOL[precision]
+    l1, dv1, da1 = _run_value_and_grad(v, a_rep, precision)
+    l2, dv2, da2 = _run_value_and_grad(v, a, precision, col_mult=t)
+    print(f"cfg4 [{precision}] repeated: dv {relnorm(dv1, dv):.2e} da {relnorm(da1, da_rep):.2e}; "
+          f"tube: dv {relnorm(dv2, dv):.2e} da {relnorm(da2, da):.2e}")
+    for l in (l1, l2):
+        assert abs(l - o["loss"]) < tol * max(1.0, abs(o["loss"]))
+    assert relnorm(dv1, dv) < gtol and relnorm(da1, da_rep) < gtol
+    assert relnorm(dv2, dv) < gtol and relnorm(da2, da) < gtol
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("n_v,n_a,off", [(64, 1024, 320), (7, 130, 60), (2, 257, 255), (33, 300, 0)])
+def test_backward_ragged_shapes_with_col_offset(n_v, n_a, off, precision):
+    """Backward with col_offset != 0 (mask column and the positive-column fix-up), ragged audio
+    counts (pad rows of the last 128 / 256-row tile) and multi-tile n_a_pad: what a rank of the
+    sharded step runs."""
+    v, a = head_features(n_v, n_a, 100 + n_v, "mix")
+    pos = off + np.arange(n_v)
+    o, dv, da = ho.head_forward_backward_torch(v, a, pos=pos)
+    tol, gtol = TOL[precision]
+    r = run_head(v, a, precision, col_offset=off, grad=True)
+    assert rel(r["logits"], o["logits"]) < tol
+    assert relnorm(r["dv"], dv) < gtol, relnorm(r["dv"], dv)
+    assert relnorm(r["da"], da) < gtol, relnorm(r["da"], da)
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_loss_rows_upstream_gradient_in_kernel(precision):
+    """A non-uniform gradient into loss_rows (<w, loss_rows>) is applied inside row_grad_kernel
+    (dloss_rows of the C ABI), not by an eager softmax on the host side."""
+    n = 40
+    v, a = head_features(n, n, 8, "mix")
+    w = np.random.default_rng(2).uniform(-0.5, 1.5, n).astype(np.float32)
+    _, dv, da = ho.head_forward_backward_torch(v, a, loss_scale=0.0, row_weights=w)
+    from audio_visual_tubes_b200 import HeadConfig, hardway_head
+    vt = torch.tensor(v, device="cuda", requires_grad=True)
+    at = torch.tensor(a, device="cuda", requires_grad=True)
+    out = hardway_head(vt, at, HeadConfig(precision=precision))
+    (torch.tensor(w, device="cuda") * out[5]).sum().backward()
+    gtol = TOL[precision][1]
+    assert relnorm(vt.grad.cpu().numpy(), dv) < gtol
+    assert relnorm(at.grad.cpu().numpy(), da) < gtol
+
+
+def test_two_host_threads_one_device():
+    """The nn.DataParallel caller of SURVEY 8b: two host threads, each on its own stream of the
+    same device, run forward + backward concurrently (the side stream / events of the backward are
+    per caller stream) and both get the single-threaded result bit for bit."""
+    import threading
+    from audio_visual_tubes_b200 import HeadConfig, hardway_value_and_grad
+    cfg = HeadConfig(precision="f16")
+    data = []
+    for seed in (3, 4):
+        v, a = head_features(48, 300, seed, "mix")
+        vt = torch.tensor(v, device="cuda"); at = torch.tensor(a, device="cuda")
+        pos = torch.arange(48, device="cuda", dtype=torch.int32) + 17
+        ref = [hardway_value_and_grad(vt, at, cfg, pos_idx=pos)[1].clone() for _ in range(1)][0]
+        data.append((vt, at, pos, ref))
+    torch.cuda.synchronize()
+    bad = []
+
+    def work(i):
+        vt, at, pos, ref = data[i]
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            for _ in range(40):
+                dv = hardway_value_and_grad(vt, at, cfg, pos_idx=pos)[1]
+                if not torch.equal(dv, ref):
+                    bad.append(i)
+        s.synchronize()
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert not bad

@@ -201,3 +201,20 @@ def test_per_video_loop_is_the_single_frame_glue_per_video():
         masks = [eo.evaluate_map(m, g, 1)["mask"] for m, g in zip(maps[v], gt[v])]
         assert o["per_video"][v, 2] == eo.mtc(masks)
     assert o["auc_mean"] == o["per_video"][:, 1].sum() / 2
+
+
+def test_eval_oracle_on_all_real_vggss_boxes():
+    """Oracle vs the UNMODIFIED reference on config 3's real data: the GT rasterisation of all 5158
+    VGG-SS box lists (pixel sums), and cIoU / AUC of the seeded maps within the 1e-3 that cv2's
+    <= 1-ulp bilinear rounding allows (tests/golden/make_golden_vggss.py made the fixture)."""
+    g = np.load(os.path.join(GOLD, "vggss_golden.npz"))
+    n = len(g["count"])
+    boxes = [g["boxes"][i, :g["count"][i]].tolist() for i in range(n)]
+    gts = [eo.rasterise_gt(b, "vggss")[0] for b in boxes]
+    assert np.array_equal(np.array([int(x.sum()) for x in gts]), g["gt_sum"])
+    idx = np.r_[0:n:7, np.nonzero(g["gt_sum"] == 0)[0], np.nonzero(g["count"] >= 4)[0]]
+    maps = eo.synthetic_maps(n, 0)
+    o = eo.evaluate_maps(maps[idx], [gts[i] for i in idx], 1)
+    ok = ~np.isnan(g["ciou"][idx])
+    assert np.abs(o["ciou"][ok] - g["ciou"][idx][ok]).max() < 1e-3
+    assert np.abs(o["inter_w"] - g["inter"][idx]).max() <= 8
