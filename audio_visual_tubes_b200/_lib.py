@@ -15,6 +15,8 @@ PRECISION_FP32 = 0
 PRECISION_F16 = 1
 GT_VGGSS, GT_FLICKR, GT_FLICKR_FRAME = 0, 1, 2
 EVAL_WORKSPACE_BYTES = 64
+DTYPE_F32, DTYPE_F16, DTYPE_BF16 = 0, 1, 2
+STAGE_PREP, STAGE_SIM, BWD_ROWGRAD_DONE = 1, 2, 1
 
 _p = C.c_void_p
 _i = C.c_int
@@ -34,10 +36,10 @@ SIGNATURES = {
     "avt_audio_normalize": (_i, [_p, _i, _i, _p, _p, _p]),
     "avt_audio_normalize_backward": (_i, [_p, _p, _p, _i, _i, _p, _p]),
     "avt_head_workspace_bytes": (_z, [_i, _i, _i, _i, _i, _i]),
-    "avt_head_forward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
-                              _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
-    "avt_head_backward": (_i, [_p, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
-                               _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
+    "avt_head_forward": (_i, [_p, _i, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
+                              _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _f, _p, _z, _p]),
+    "avt_head_backward": (_i, [_p, _i, _p, _i, _i, _i, _i, _p, _i, _f, _f, _f, _f, _f, _i, _i, _i, _i,
+                               _p, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _i, _p, _p, _z, _p]),
     "avt_eval_maps": (_i, [_p, _i, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
     "avt_eval_stats": (_i, [_p, _i]),
     "avt_ciou_counts": (_i, [_p, _f, _p, _i, _i, _p, _p, _p, _p]),

@@ -28,6 +28,7 @@ struct ProfState {
 static ProfState g_prof[kProfSlots];
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+bool prof_enabled() { return g_prof_on.load(std::memory_order_relaxed) != 0; }
 
 void prof_begin(int slot, cudaStream_t st) {
     if (!g_prof_on.load(std::memory_order_relaxed)) return;

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
+#include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include "../../include/avtubes.h"
@@ -21,6 +22,7 @@ enum ProfSlot {
     kProfBwdDv = 5, kProfBwdDa = 6, kProfDvFinish = 7, kProfEval = 8, kProfSlots = 9
 };
 void count_launch();
+bool prof_enabled();
 void prof_begin(int slot, cudaStream_t st);
 void prof_end(int slot, cudaStream_t st);
 struct ProfScope {
@@ -121,13 +123,14 @@ __device__ __forceinline__ float pow2i(int e) { return __int_as_float((e + 127) 
 
 // ---- kernel launchers implemented in the .cu files -------------------------------
 // prep: rnorm_v, A (positive map), msum (mean_c v_hat), optional fp16 K-major copy
-int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_idx, int col_offset,
+int launch_prep_visual(const void* v, int v_dtype, const float* a_hat, const int32_t* pos_idx, int col_offset,
                        int N_v, int N_a, int C, int P, float* rnorm_v, float* A, float* msum,
                        __half* vt_f16, HeadScratch* scratch, cudaStream_t st);
 int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int P, HeadParams hp,
                        float* Pos, float* Neg, float* weighted_A, float* logits,
                        float* loss_rows, float* loss_sum, HeadScratch* scratch, const int32_t* pos_idx,
-                       int col_offset, const float* sim, int col_mult, cudaStream_t st);
+                       int col_offset, const float* sim, int col_mult, float fuse_scale, float* gsim,
+                       float* GA, const float* den, unsigned int* gmax_bits, cudaStream_t st);
 int launch_sim_fp32(const float* v, const float* a_hat, const float* rnorm_v,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                     HeadParams hp, float* logits, float* sim, float* den, cudaStream_t st);
@@ -158,7 +161,7 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h, __half* 
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C,
                     int P, HeadParams hp, const float* sim, const float* den, const float* gsim,
                     const float* GA, float* dv, float* d_ahat, const unsigned int* gmax_bits,
-                    cudaStream_t st);
+                    cudaStream_t dv_stream, cudaStream_t st);
 int launch_audio_to_f16(const float* a_hat, int N_a, int N_a_pad, int C, __half* out,
                          cudaStream_t st);
 

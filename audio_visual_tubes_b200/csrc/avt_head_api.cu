@@ -62,24 +62,32 @@ extern "C" size_t avt_head_workspace_bytes(int N_v, int N_a, int C, int P, int p
     return head_workspace_layout(N_v, N_a, C, P, precision, backward).total;
 }
 
-extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int N_a, int C, int P,
+extern "C" int avt_head_forward(const void* v_any, int v_dtype, const float* a_hat, int N_v, int N_a, int C, int P,
                                 const int32_t* pos_idx, int col_offset, float eps, float eps2,
                                 float tau, float temp, float mask_scale, int trimap, int use_neg,
                                 int precision, int col_mult, float* A, float* Pos, float* Neg, float* logits,
                                 float* loss_rows, float* loss_sum, float* weighted_A,
-                                float* rnorm_v, float* sim, float* den, void* workspace,
+                                float* rnorm_v, float* sim, float* den, int stages,
+                                float fuse_grad_scale, void* workspace,
                                 size_t workspace_bytes, void* stream) {
     int rc = check_shapes("avt_head_forward", N_v, N_a, C, P, precision);
     if (rc != AVT_OK) return rc;
-    AVT_REQUIRE(v && a_hat && A && Pos && Neg && logits && loss_rows && rnorm_v && sim && den,
+    AVT_REQUIRE(v_any && a_hat && A && Pos && Neg && logits && loss_rows && rnorm_v && sim && den,
                 "avt_head_forward: null pointer among required arguments");
+    AVT_REQUIRE(v_dtype == AVT_DTYPE_F32 || ((v_dtype == AVT_DTYPE_F16 || v_dtype == AVT_DTYPE_BF16) &&
+                                             precision == AVT_PRECISION_F16),
+                "avt_head_forward: v_dtype=%d (fp16 / bf16 maps need AVT_PRECISION_F16)", v_dtype);
+    const float* v = static_cast<const float*>(v_any);      // only dereferenced when v_dtype is fp32
     AVT_REQUIRE(tau > 0.f && temp > 0.f, "avt_head_forward: tau and temp must be positive");
     AVT_REQUIRE(col_mult >= 1, "avt_head_forward: col_mult=%d must be >= 1", col_mult);
     AVT_REQUIRE(col_mult == 1 || pos_idx != nullptr,
                 "avt_head_forward: tube mode (col_mult > 1) needs pos_idx (the audio row of every frame)");
     AVT_REQUIRE(workspace != nullptr, "avt_head_forward: workspace is null");
+    AVT_REQUIRE(stages >= 0 && stages <= 3, "avt_head_forward: stages=%d", stages);
+    if (stages == 0) stages = AVT_STAGE_PREP | AVT_STAGE_SIM;
+    const bool fuse = fuse_grad_scale != 0.0f && (stages & AVT_STAGE_SIM);
     // the forward regions lead both layouts, so a workspace sized for backward works too
-    HeadWorkspace w = head_workspace_layout(N_v, N_a, C, P, precision, 0);
+    HeadWorkspace w = head_workspace_layout(N_v, N_a, C, P, precision, fuse ? 1 : 0);
     if (workspace_bytes < w.total) {
         set_error("avt_head_forward: workspace %zu B < required %zu B", workspace_bytes, w.total);
         return AVT_ERR_WORKSPACE;
@@ -90,34 +98,44 @@ extern "C" int avt_head_forward(const float* v, const float* a_hat, int N_v, int
     HeadScratch* scratch = reinterpret_cast<HeadScratch*>(ws + w.scratch);
     float* msum = reinterpret_cast<float*>(ws + w.msum);
 
-    if (precision == AVT_PRECISION_FP32) {
-        rc = launch_prep_visual(v, a_hat, pos_idx, col_offset, N_v, N_a, C, P, rnorm_v, A, msum,
-                                nullptr, scratch, st);
+    if (precision == AVT_PRECISION_F16 && !avt_device_ok()) {
+        set_error("avt_head_forward: the fp16 tcgen05 path needs an sm_100 device");
+        return AVT_ERR_UNSUPPORTED;
+    }
+    __half* vt = precision == AVT_PRECISION_F16 ? reinterpret_cast<__half*>(ws + w.vt) : nullptr;
+    if (stages & AVT_STAGE_PREP) {
+        rc = launch_prep_visual(v_any, v_dtype, a_hat, pos_idx, col_offset, N_v, N_a, C, P, rnorm_v, A, msum, vt,
+                                scratch, st);
         if (rc != AVT_OK) return rc;
+    }
+    if (!(stages & AVT_STAGE_SIM)) return AVT_OK;
+    if (precision == AVT_PRECISION_FP32) {
         rc = launch_sim_fp32(v, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim,
                              den, st);
         if (rc != AVT_OK) return rc;
     } else {
-        if (!avt_device_ok()) {
-            set_error("avt_head_forward: the fp16 tcgen05 path needs an sm_100 device");
-            return AVT_ERR_UNSUPPORTED;
-        }
-        __half* vt = reinterpret_cast<__half*>(ws + w.vt);
         __half* a_h = reinterpret_cast<__half*>(ws + w.a_h);
         const int n_a_pad = n_a_padded(N_a);
         rc = launch_audio_to_f16(a_hat, N_a, n_a_pad, C, a_h, st);
         if (rc != AVT_OK) return rc;
-        rc = launch_prep_visual(v, a_hat, pos_idx, col_offset, N_v, N_a, C, P, rnorm_v, A, msum, vt,
-                                scratch, st);
-        if (rc != AVT_OK) return rc;
         rc = launch_sim_f16(vt, a_h, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den, st);
         if (rc != AVT_OK) return rc;
     }
+    float* gsim = nullptr; float* GA = nullptr; unsigned int* gmax_bits = nullptr;
+    if (fuse) {             // fused training step: the row gradients come out of the finish kernel
+        gsim = reinterpret_cast<float*>(ws + w.gsim);
+        GA = reinterpret_cast<float*>(ws + w.ga);
+        if (precision == AVT_PRECISION_F16) {
+            gmax_bits = &scratch->gmax_bits;
+            AVT_CHECK_CUDA(cudaMemsetAsync(gmax_bits, 0, sizeof(unsigned int), st));
+        }
+    }
     return launch_finish_rows(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A, logits, loss_rows,
-                              loss_sum, scratch, pos_idx, col_offset, sim, col_mult, st);
+                              loss_sum, scratch, pos_idx, col_offset, sim, col_mult, fuse_grad_scale, gsim, GA,
+                              den, gmax_bits, st);
 }
 
-extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, int N_a, int C, int P,
+extern "C" int avt_head_backward(const void* v_any, int v_dtype, const float* a_hat, int N_v, int N_a, int C, int P,
                                  const int32_t* pos_idx, int col_offset, float eps, float eps2,
                                  float tau, float temp, float mask_scale, int trimap, int use_neg,
                                  int precision, int col_mult, const float* A, const float* logits,
@@ -125,12 +143,16 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
                                  const float* den, float dloss_scale, const float* dloss_rows,
                                  const float* dlogits,
                                  const float* dA, const float* dWeighted, float* dv,
-                                 float* d_ahat, void* workspace,
+                                 float* d_ahat, int flags, void* dv_stream, void* workspace,
                                  size_t workspace_bytes, void* stream) {
     int rc = check_shapes("avt_head_backward", N_v, N_a, C, P, precision);
     if (rc != AVT_OK) return rc;
-    AVT_REQUIRE(v && a_hat && A && logits && loss_rows && rnorm_v && sim && den && dv && d_ahat,
+    AVT_REQUIRE(v_any && a_hat && A && logits && loss_rows && rnorm_v && sim && den && dv && d_ahat,
                 "avt_head_backward: null pointer among required arguments");
+    AVT_REQUIRE(v_dtype == AVT_DTYPE_F32 || ((v_dtype == AVT_DTYPE_F16 || v_dtype == AVT_DTYPE_BF16) &&
+                                             precision == AVT_PRECISION_F16 && dWeighted == nullptr),
+                "avt_head_backward: v_dtype=%d (fp16 / bf16 maps need AVT_PRECISION_F16 and no dWeighted)", v_dtype);
+    const float* v = static_cast<const float*>(v_any);      // the fp16 path never reads it (uses its own copy)
     AVT_REQUIRE(workspace != nullptr, "avt_head_backward: workspace is null");
     AVT_REQUIRE(col_mult >= 1 && (col_mult == 1 || pos_idx != nullptr),
                 "avt_head_backward: col_mult=%d (tube mode needs pos_idx)", col_mult);
@@ -154,14 +176,19 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
         dA = da_w;
     }
     HeadScratch* scratch = reinterpret_cast<HeadScratch*>(ws + w.scratch);
-    unsigned int* gmax_bits = nullptr;
-    if (precision == AVT_PRECISION_F16) {          // bound of the cell gradients -> fp16 scale of G
-        gmax_bits = &scratch->gmax_bits;
-        AVT_CHECK_CUDA(cudaMemsetAsync(gmax_bits, 0, sizeof(unsigned int), st));
+    unsigned int* gmax_bits = precision == AVT_PRECISION_F16 ? &scratch->gmax_bits : nullptr;
+    if (flags & AVT_BWD_ROWGRAD_DONE) {
+        // the forward ran with fuse_grad_scale: gsim / GA / the bound of G are in the workspace
+        AVT_REQUIRE(!dlogits && !dA && !dWeighted && !dloss_rows,
+                    "avt_head_backward: AVT_BWD_ROWGRAD_DONE takes no upstream tensors (the fused forward "
+                    "already applied fuse_grad_scale)");
+    } else {
+        if (gmax_bits)                             // bound of the cell gradients -> fp16 scale of G
+            AVT_CHECK_CUDA(cudaMemsetAsync(gmax_bits, 0, sizeof(unsigned int), st));
+        rc = launch_row_grad(A, logits, loss_rows, pos_idx, col_offset, N_v, N_a, P, hp, dloss_scale,
+                             dlogits, dA, gsim, GA, sim, col_mult, dloss_rows, den, gmax_bits, st);
+        if (rc != AVT_OK) return rc;
     }
-    rc = launch_row_grad(A, logits, loss_rows, pos_idx, col_offset, N_v, N_a, P, hp, dloss_scale,
-                         dlogits, dA, gsim, GA, sim, col_mult, dloss_rows, den, gmax_bits, st);
-    if (rc != AVT_OK) return rc;
     AVT_CHECK_CUDA(cudaMemsetAsync(d_ahat, 0, (size_t)N_a * C * sizeof(float), st));
     if (precision == AVT_PRECISION_FP32) {
         AVT_CHECK_CUDA(cudaMemsetAsync(dv, 0, (size_t)N_v * C * P * sizeof(float), st));
@@ -182,7 +209,8 @@ extern "C" int avt_head_backward(const float* v, const float* a_hat, int N_v, in
     __half* at_h = reinterpret_cast<__half*>(ws + w.at_h);
     __half* g_h = reinterpret_cast<__half*>(ws + w.g_h);
     rc = launch_bwd_f16(v, vt, a_h, at_h, g_h, a_hat, rnorm_v, pos_idx, col_offset, N_v, N_a,
-                         n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, gmax_bits, st);
+                         n_a_pad, C, P, hp, sim, den, gsim, GA, dv, d_ahat, gmax_bits,
+                         static_cast<cudaStream_t>(dv_stream), st);
     if (rc != AVT_OK || !dWeighted) return rc;
     return launch_weighted_dv(v, rnorm_v, msum, u_w, N_v, C, P, dv, st);
 }

@@ -4,6 +4,7 @@
 // weighted_A, cross-entropy).  HBM-bound kernels: coalesced along P, 16 independent
 // loads in flight per thread.
 #include "avt_common.cuh"
+#include "avt_rows.cuh"
 
 namespace avt {
 
@@ -70,9 +71,15 @@ constexpr int kPrepMaxCpw = 32;                  // channels per warp, C <= 512
 
 // kC / kP: compile-time C and P of the reference's shapes (512 channels, 14 x 14 positions) so that
 // every guard folds and every load / store offset is an immediate; 0 = take the run-time value.
-template <bool kWriteF16, int kC, int kP>
+// TIn: element type of the caller's maps -- fp32 from the reference's fp32 backbones, or fp16 / bf16
+// when the backbone ran under autocast (halves the bytes of this pass and of a host->device copy).
+__device__ __forceinline__ float ld_in(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float ld_in(const __half* p) { return __half2float(__ldg(p)); }
+__device__ __forceinline__ float ld_in(const __nv_bfloat16* p) { return __bfloat162float(__ldg(p)); }
+
+template <bool kWriteF16, int kC, int kP, typename TIn>
 __global__ void __launch_bounds__(kPrepThreads, 2)
-prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
+prep_visual_kernel(const TIn* __restrict__ v, const float* __restrict__ a_hat,
                    const int32_t* __restrict__ pos_idx, int col_offset, int N_a, int C_rt, int P_rt,
                    float* __restrict__ rnorm_v, float* __restrict__ A, float* __restrict__ msum,
                    __half* __restrict__ vt, HeadScratch* scratch) {
@@ -93,10 +100,10 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
         s_a[c] = has_pos ? a_hat[(size_t)pos * C + c] : 0.f;
 
     float x[kPrepMaxCpw];
-    const float* vp = v + ((size_t)n * C + (size_t)w * cpw) * P + p;
+    const TIn* vp = v + ((size_t)n * C + (size_t)w * cpw) * P + p;
 #pragma unroll
     for (int i = 0; i < kPrepMaxCpw; ++i)
-        x[i] = (active && i < cpw) ? __ldg(vp + (size_t)i * P) : 0.f;
+        x[i] = (active && i < cpw) ? ld_in(vp + (size_t)i * P) : 0.f;
     __syncthreads();                         // s_a ready
     float ssq = 0.f, dot = 0.f, sum = 0.f;
 #pragma unroll
@@ -162,7 +169,7 @@ prep_visual_kernel(const float* __restrict__ v, const float* __restrict__ a_hat,
     }
 }
 
-int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_idx, int col_offset,
+int launch_prep_visual(const void* v_any, int v_dtype, const float* a_hat, const int32_t* pos_idx, int col_offset,
                        int N_v, int N_a, int C, int P, float* rnorm_v, float* A, float* msum,
                        __half* vt_f16, HeadScratch* scratch, cudaStream_t st) {
     ProfScope _ps(kProfPrep, st);
@@ -170,11 +177,17 @@ int launch_prep_visual(const float* v, const float* a_hat, const int32_t* pos_id
     dim3 grid((P + 31) / 32, N_v);
     size_t smem = (size_t)(C + 3 * kPrepWarps * 32) * sizeof(float) + (vt_f16 ? (size_t)32 * (C * 2 + 16) : 0);
     const bool ref_shape = (C == 512 && P == 196);
-#define AVT_PREP(BF, KC, KP)                                                                        \
-    prep_visual_kernel<BF, KC, KP><<<grid, kPrepThreads, smem, st>>>(v, a_hat, pos_idx, col_offset, N_a, C, P, \
-                                                                     rnorm_v, A, msum, vt_f16, scratch)
-    if (vt_f16) { if (ref_shape) AVT_PREP(true, 512, 196); else AVT_PREP(true, 0, 0); }
-    else { if (ref_shape) AVT_PREP(false, 512, 196); else AVT_PREP(false, 0, 0); }
+#define AVT_PREP(BF, KC, KP, T)                                                                     \
+    prep_visual_kernel<BF, KC, KP, T><<<grid, kPrepThreads, smem, st>>>(static_cast<const T*>(v_any), a_hat, pos_idx, \
+                                                                        col_offset, N_a, C, P, rnorm_v, A, msum, vt_f16, scratch)
+    if (v_dtype == AVT_DTYPE_F32) {
+        if (vt_f16) { if (ref_shape) AVT_PREP(true, 512, 196, float); else AVT_PREP(true, 0, 0, float); }
+        else { if (ref_shape) AVT_PREP(false, 512, 196, float); else AVT_PREP(false, 0, 0, float); }
+    } else {
+        AVT_REQUIRE(vt_f16 != nullptr, "prep: fp16 / bf16 maps are taken by the tensor-core path only");
+        if (v_dtype == AVT_DTYPE_F16) { if (ref_shape) AVT_PREP(true, 512, 196, __half); else AVT_PREP(true, 0, 0, __half); }
+        else { if (ref_shape) AVT_PREP(true, 512, 196, __nv_bfloat16); else AVT_PREP(true, 0, 0, __nv_bfloat16); }
+    }
 #undef AVT_PREP
     AVT_LAUNCH_CHECK();
     return AVT_OK;
@@ -214,7 +227,9 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
                    float* __restrict__ weighted_A, float* __restrict__ logits,
                    float* __restrict__ loss_rows, float* __restrict__ loss_sum,
                    HeadScratch* scratch, const int32_t* __restrict__ pos_idx, int col_offset,
-                   const float* __restrict__ sim, int col_mult) {
+                   const float* __restrict__ sim, int col_mult,
+                   float fuse_scale, float* __restrict__ gsim, float* __restrict__ GA,
+                   const float* __restrict__ den, unsigned int* __restrict__ gmax_bits) {
     __shared__ float s_tmp[kRowThreads / 32];
     __shared__ float s_multi[kRowThreads / 32][5];
     __shared__ bool s_last;
@@ -292,6 +307,13 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
     s = block_sum(s, s_tmp);
     if (threadIdx.x == 0) loss_rows[n] = (m + logf(s)) - l_first;
 
+    // fused training step (gsim != NULL): the row's upstream gradients right here -- the softmax
+    // needs nothing but this row's log-sum-exp, so the separate row_grad_kernel launch (12-18 us,
+    // fixed, on the critical path of small shards) disappears
+    if (gsim != nullptr)
+        row_grad_row(n, m + logf(s), l_first, l_last, A, logits, pos_idx, col_offset, N_a, P, hp, fuse_scale,
+                     nullptr, nullptr, gsim, GA, sim, col_mult, nullptr, den, gmax_bits);
+
     if (loss_sum == nullptr) return;
     // deterministic total: the last block to finish adds the rows in index order
     __threadfence();
@@ -311,11 +333,14 @@ finish_rows_kernel(const float* __restrict__ A, const float* __restrict__ msum, 
 int launch_finish_rows(const float* A, const float* msum, int N_v, int N_a, int P, HeadParams hp,
                        float* Pos, float* Neg, float* weighted_A, float* logits,
                        float* loss_rows, float* loss_sum, HeadScratch* scratch, const int32_t* pos_idx,
-                       int col_offset, const float* sim, int col_mult, cudaStream_t st) {
+                       int col_offset, const float* sim, int col_mult, float fuse_scale, float* gsim,
+                       float* GA, const float* den, unsigned int* gmax_bits, cudaStream_t st) {
     ProfScope _ps(kProfFinish, st);
+    static_assert(kRowThreads == kRowGradThreads, "fused row gradients share the block shape");
     finish_rows_kernel<<<N_v, kRowThreads, 0, st>>>(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A,
                                                     logits, loss_rows, loss_sum, scratch, pos_idx,
-                                                    col_offset, sim, col_mult);
+                                                    col_offset, sim, col_mult, fuse_scale, gsim, GA, den,
+                                                    gmax_bits);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }

@@ -708,7 +708,7 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
                     const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_a_pad, int C, int P,
                     HeadParams hp, const float* sim, const float* den, const float* gsim,
                     const float* GA, float* dv, float* d_ahat, const unsigned int* gmax_bits,
-                    cudaStream_t st) {
+                    cudaStream_t dv_stream, cudaStream_t st) {
     (void)a_hat; (void)v;
     AVT_REQUIRE(C % 64 == 0 && C <= 512, "fp16 backward: C=%d must be a multiple of 64, <= 512", C);
     const int n_rows = N_v * P;
@@ -716,35 +716,45 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
     AVT_CHECK_CUDA(cudaGetDevice(&dev));
     AVT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 
-    // the side stream first transposes the audio operand of stage 2 while stage 1 runs, then (after
-    // stage 1) carries stage 3 concurrently with stage 2
+    // Stage 2 (dv) and stage 3 (d_ahat) both consume G and are independent.  Two ways to overlap them:
+    //  * caller-provided dv_stream: dv (and the audio transpose it needs) go THERE, d_ahat stays on
+    //    `st`, and nothing is joined here -- the sharded step starts its reduce_scatter of d_ahat the
+    //    moment stage 3 is done, under the dv kernel, and joins dv_stream when it needs dv;
+    //  * otherwise an internal side stream carries the transpose and stage 3 and is joined back
+    //    into `st` before this function returns.
+    // With stage profiling on, everything runs on `st` so that the stage times are those of the
+    // kernels alone.
     const EnvSwitches& env = env_switches();
-    SideStream* side = env.no_side ? nullptr : side_stream(dev, st);
-    cudaStream_t st_da = side ? side->stream : st;
-    SideJoin joiner{side, st};
+    const bool serial = prof_enabled() || env.no_side;
+    SideStream* side = serial ? nullptr : side_stream(dev, st);
+    const bool ext = side && dv_stream && dv_stream != st;
+    cudaStream_t st_dv = ext ? dv_stream : st;
+    cudaStream_t st_da = (side && !ext) ? side->stream : st;
+    cudaStream_t st_tr = ext ? dv_stream : st_da;        // stream of the audio transpose
+    SideJoin joiner{ext ? nullptr : side, st};
     if (side) {
         AVT_CHECK_CUDA(cudaEventRecord(side->fork0, st));
-        AVT_CHECK_CUDA(cudaStreamWaitEvent(side->stream, side->fork0, 0));
+        AVT_CHECK_CUDA(cudaStreamWaitEvent(st_tr, side->fork0, 0));
         joiner.forked = true;
     }
     {
         dim3 grid(n_a_pad / 32, C / 32), block(32, 8);
-        transpose_audio_kernel<<<grid, block, 0, st_da>>>(a_h, n_a_pad, C, at_h);
+        transpose_audio_kernel<<<grid, block, 0, st_tr>>>(a_h, n_a_pad, C, at_h);
         AVT_LAUNCH_CHECK();
     }
-    if (side) AVT_CHECK_CUDA(cudaEventRecord(side->tdone, side->stream));
+    if (side && !ext) AVT_CHECK_CUDA(cudaEventRecord(side->tdone, side->stream));
     // stage 1: cell gradients
     int rc = launch_grad_cells_f16(vt, a_h, pos_idx, col_offset, N_v, N_a, n_a_pad, C, P, hp, sim, den,
                                     gsim, GA, g_h, gmax_bits, st);
     if (rc != AVT_OK) return rc;
     if (side) {
-        AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->tdone, 0));
+        if (!ext) AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->tdone, 0));
         AVT_CHECK_CUDA(cudaEventRecord(side->fork, st));
-        AVT_CHECK_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
+        AVT_CHECK_CUDA(cudaStreamWaitEvent(ext ? st_dv : side->stream, side->fork, 0));
     }
     // stage 2: dv
     {
-        ProfScope _ps(kProfBwdDv, st);
+        ProfScope _ps(kProfBwdDv, st_dv);
         const bool pair = (C == 256 || C == 512) && !env.no_pair;
         CUtensorMap map_g, map_at;
         if (!make_tmap_f16_2d(&map_g, g_h, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, kDvBM) ||
@@ -758,13 +768,13 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
             const int grid_pairs = n_pairs < sms / 2 ? n_pairs : sms / 2;
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDv2SmemBytes));
-            bwd_dv_pair_kernel<<<2 * grid_pairs, kDvThreads, kDv2SmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv,
+            bwd_dv_pair_kernel<<<2 * grid_pairs, kDvThreads, kDv2SmemBytes, st_dv>>>(map_g, map_at, vt, rnorm_v, dv,
                                                                                   n_rows, n_pairs, n_a_pad / kDvBK, C, P, gmax_bits);
         } else {
             const int grid = n_tiles < sms ? n_tiles : sms;
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDvSmemBytes));
-            bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st>>>(map_g, map_at, vt, rnorm_v, dv, n_rows,
+            bwd_dv_kernel<<<grid, kDvThreads, kDvSmemBytes, st_dv>>>(map_g, map_at, vt, rnorm_v, dv, n_rows,
                                                                  n_tiles, n_a_pad / kDvBK, C, P, gmax_bits);
         }
         AVT_LAUNCH_CHECK();

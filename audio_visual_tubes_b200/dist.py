@@ -21,8 +21,8 @@ from __future__ import annotations
 import torch
 import torch.distributed as dist
 
-from .head import (HeadConfig, audio_normalize, audio_normalize_backward, head_backward_raw,
-                   head_forward_raw)
+from .head import (HeadConfig, as_head_input, audio_normalize, audio_normalize_backward,
+                   head_backward_raw, head_forward_raw)
 
 
 def _lib_compute():
@@ -128,20 +128,21 @@ def sharded_value_and_grad(v, a, cfg: HeadConfig = HeadConfig(), group=None, wan
     ``(global mean loss [1], dv_local, da_local)``; see ``sharded_hardway_loss``."""
     if v.dim() == 4:
         v = v.flatten(2)
-    v = v.contiguous().float()
+    v = as_head_input(v, cfg)
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     b_local = a.shape[0]
     a_hat_local, rn_local = audio_normalize(a.contiguous().float())
     a_hat = torch.empty(world * b_local, a.shape[1], device=a.device, dtype=torch.float32)
     dist.all_gather_into_tensor(a_hat, a_hat_local, group=group)
-    out = head_forward_raw(v, a_hat, cfg, None, rank * b_local, False, for_backward=want_grad)
+    scale = 1.0 / float(world * b_local)
+    out = head_forward_raw(v, a_hat, cfg, None, rank * b_local, False, for_backward=want_grad,
+                           fuse_grad_scale=scale if want_grad else 0.0)
     total = out["loss_sum"].clone()
     dist.all_reduce(total, group=group)
     loss = total / float(world * b_local)
     if not want_grad:
         return loss, None, None
-    dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 1.0 / float(world * b_local), None, None,
-                                   rank * b_local)
+    dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 0.0, None, None, rank * b_local, rowgrad_done=True)
     d_local = torch.empty_like(a_hat_local)
     dist.reduce_scatter_tensor(d_local, d_ahat, group=group)
     da = audio_normalize_backward(a_hat_local, rn_local, d_local)

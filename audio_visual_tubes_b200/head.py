@@ -18,6 +18,16 @@ import torch
 from . import _lib
 
 PRECISION = {"fp32": _lib.PRECISION_FP32, "f16": _lib.PRECISION_F16}
+V_DTYPE = {torch.float32: _lib.DTYPE_F32, torch.float16: _lib.DTYPE_F16, torch.bfloat16: _lib.DTYPE_BF16}
+
+
+def as_head_input(v: torch.Tensor, cfg) -> torch.Tensor:
+    """The visual maps as the kernels take them: contiguous, fp32 -- or fp16 / bf16 left as they are
+    on the tensor-core path (a backbone under autocast emits them; the prep pass reads half the
+    bytes and a host->device copy moves half of them)."""
+    if v.dtype in (torch.float16, torch.bfloat16) and cfg.precision == "f16":
+        return v.contiguous()
+    return v.contiguous().float()
 
 
 @dataclass(frozen=True)
@@ -59,49 +69,63 @@ def audio_normalize_backward(a_hat, rnorm_a, d_ahat):
 
 
 def head_forward_raw(v, a_hat, cfg: HeadConfig, pos_idx=None, col_offset=0, want_weighted=False,
-                     for_backward=False, col_mult=1):
+                     for_backward=False, col_mult=1, fuse_grad_scale=0.0, stages=0, out=None, n_a_total=None):
     """One ``avt_head_forward`` call.  ``a_hat`` must already be L2-normalised rows.
     Returns a dict of output tensors (+ the workspace to hand to the backward).
     ``col_mult = T > 1``: tube mode, ``a_hat`` holds the DISTINCT audio rows, each standing for T
-    identical logit columns (see include/avtubes.h); ``logits`` is then the compact row."""
+    identical logit columns (see include/avtubes.h); ``logits`` is then the compact row.
+    ``fuse_grad_scale != 0``: fused training step, the row gradients of ``fuse_grad_scale * sum(loss_rows)``
+    are produced by the forward; call ``head_backward_raw(..., rowgrad_done=True)``.
+    ``stages`` / ``out`` / ``n_a_total``: split forward for row-sharded callers -- run
+    ``stages=STAGE_PREP`` with the rank's own audio rows (``n_a_total`` = the global count, which
+    sizes the outputs and the workspace), then ``stages=STAGE_SIM`` with the gathered rows and
+    ``out=`` the dict the first call returned."""
     _lib.require_cuda(v, a_hat)
     lib = _lib.load()
-    assert v.dtype == torch.float32 and a_hat.dtype == torch.float32
+    assert v.dtype in V_DTYPE and a_hat.dtype == torch.float32
     assert v.is_contiguous() and a_hat.is_contiguous()
     n_v, c, p = v.shape
     n_a = a_hat.shape[0]
+    n_all = int(n_a_total or n_a)                 # sizes outputs / workspace (split forward: global count)
     dev = v.device
-    L = n_a + 1 + (1 if cfg.use_neg else 0)
     prec = PRECISION[cfg.precision]
-    f32 = dict(device=dev, dtype=torch.float32)
-    out = dict(
-        A=torch.empty(n_v, p, **f32), Pos=torch.empty(n_v, p, **f32), Neg=torch.empty(n_v, p, **f32),
-        logits=torch.empty(n_v, L, **f32), loss_rows=torch.empty(n_v, **f32),
-        loss_sum=torch.empty(1, **f32), rnorm_v=torch.empty(n_v, p, **f32),
-        sim=torch.empty(n_v, n_a, **f32), den=torch.empty(n_v, n_a, **f32),
-        weighted_A=torch.empty(n_v, p, **f32) if want_weighted else None)
-    nbytes = lib.avt_head_workspace_bytes(n_v, n_a, c, p, prec, 1 if for_backward else 0)
-    ws = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    if out is None:
+        L = n_all + 1 + (1 if cfg.use_neg else 0)
+        f32 = dict(device=dev, dtype=torch.float32)
+        out = dict(
+            A=torch.empty(n_v, p, **f32), Pos=torch.empty(n_v, p, **f32), Neg=torch.empty(n_v, p, **f32),
+            logits=torch.empty(n_v, L, **f32), loss_rows=torch.empty(n_v, **f32),
+            loss_sum=torch.empty(1, **f32), rnorm_v=torch.empty(n_v, p, **f32),
+            sim=torch.empty(n_v, n_all, **f32), den=torch.empty(n_v, n_all, **f32),
+            weighted_A=torch.empty(n_v, p, **f32) if want_weighted else None)
+        nbytes = lib.avt_head_workspace_bytes(n_v, n_all, c, p, prec,
+                                              1 if (for_backward or fuse_grad_scale) else 0)
+        out["workspace"] = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    ws = out["workspace"]
+    nbytes = ws.numel()
     if pos_idx is not None:
         pos_idx = pos_idx.to(device=dev, dtype=torch.int32).contiguous()
     with torch.cuda.device(dev):
         rc = lib.avt_head_forward(
-            _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(pos_idx), int(col_offset),
+            _lib.ptr(v), V_DTYPE[v.dtype], _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(pos_idx), int(col_offset),
             cfg.eps, cfg.eps2, cfg.tau, cfg.temp, cfg.mask_scale, int(cfg.trimap), int(cfg.use_neg),
             prec, int(col_mult), _lib.ptr(out["A"]), _lib.ptr(out["Pos"]), _lib.ptr(out["Neg"]),
             _lib.ptr(out["logits"]), _lib.ptr(out["loss_rows"]), _lib.ptr(out["loss_sum"]),
             _lib.ptr(out["weighted_A"]), _lib.ptr(out["rnorm_v"]), _lib.ptr(out["sim"]),
-            _lib.ptr(out["den"]), _lib.ptr(ws), C.c_size_t(nbytes), _lib.stream_ptr())
+            _lib.ptr(out["den"]), int(stages), float(fuse_grad_scale), _lib.ptr(ws), C.c_size_t(nbytes),
+            _lib.stream_ptr())
     _lib.check(rc, "avt_head_forward")
-    out["workspace"] = ws
     out["pos_idx"] = pos_idx
     out["col_mult"] = int(col_mult)
     return out
 
 
 def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits=None, dA=None,
-                      col_offset=0, dW=None, dloss_rows=None):
-    """One ``avt_head_backward`` call.  Returns (dv [N_v,C,P], d_ahat [N_a,C])."""
+                      col_offset=0, dW=None, dloss_rows=None, rowgrad_done=False, dv_stream=None):
+    """One ``avt_head_backward`` call.  Returns (dv [N_v,C,P], d_ahat [N_a,C]).
+    ``rowgrad_done``: the forward ran with ``fuse_grad_scale``.  ``dv_stream`` (torch.cuda.Stream):
+    the dv contraction runs there and ``d_ahat`` is complete on the current stream without waiting
+    for it; the caller orders ``dv_stream`` before consumers of ``dv``."""
     lib = _lib.load()
     n_v, c, p = v.shape
     n_a = a_hat.shape[0]
@@ -110,7 +134,7 @@ def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits
     need = lib.avt_head_workspace_bytes(n_v, n_a, c, p, prec, 1)
     if ws.numel() < need:
         raise RuntimeError("head_backward_raw: the forward was not run with for_backward=True")
-    dv = torch.empty_like(v)
+    dv = torch.empty(v.shape, device=v.device, dtype=torch.float32)      # always fp32, whatever v is
     d_ahat = torch.empty_like(a_hat)
     if dlogits is not None:
         dlogits = dlogits.contiguous().float()
@@ -122,13 +146,14 @@ def head_backward_raw(v, a_hat, cfg: HeadConfig, saved, dloss_scale=0.0, dlogits
         dloss_rows = dloss_rows.contiguous().float().view(n_v)
     with torch.cuda.device(v.device):
         rc = lib.avt_head_backward(
-            _lib.ptr(v), _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(saved["pos_idx"]), int(col_offset),
+            _lib.ptr(v), V_DTYPE[v.dtype], _lib.ptr(a_hat), n_v, n_a, c, p, _lib.ptr(saved["pos_idx"]), int(col_offset),
             cfg.eps, cfg.eps2, cfg.tau, cfg.temp, cfg.mask_scale, int(cfg.trimap), int(cfg.use_neg),
             prec, int(saved.get("col_mult", 1)), _lib.ptr(saved["A"]), _lib.ptr(saved["logits"]),
             _lib.ptr(saved["loss_rows"]),
             _lib.ptr(saved["rnorm_v"]), _lib.ptr(saved["sim"]), _lib.ptr(saved["den"]),
             float(dloss_scale), _lib.ptr(dloss_rows), _lib.ptr(dlogits), _lib.ptr(dA), _lib.ptr(dW), _lib.ptr(dv),
-            _lib.ptr(d_ahat),
+            _lib.ptr(d_ahat), _lib.BWD_ROWGRAD_DONE if rowgrad_done else 0,
+            None if dv_stream is None else C.c_void_p(dv_stream.cuda_stream),
             _lib.ptr(ws), C.c_size_t(ws.numel()), _lib.stream_ptr())
     _lib.check(rc, "avt_head_backward")
     return dv, d_ahat
@@ -183,7 +208,8 @@ class _HardWayHead(torch.autograd.Function):
     def forward(ctx, v, a, cfg, pos_idx, col_offset, want_weighted, col_mult=1, copy_idx=None):
         need_grad = v.requires_grad or a.requires_grad
         ctx.set_materialize_grads(False)      # unused outputs arrive as None, not as zero tensors
-        v = v.contiguous().float()
+        ctx.v_dtype = v.dtype
+        v = as_head_input(v, cfg)
         a_hat, rn_a = audio_normalize(a)
         out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, want_weighted, for_backward=need_grad,
                                col_mult=col_mult)
@@ -212,7 +238,7 @@ class _HardWayHead(torch.autograd.Function):
                                        ctx.col_offset, gW if ctx.want_weighted else None,
                                        dloss_rows=gloss_rows)
         da = audio_normalize_backward(a_hat, rn_a, d_ahat)
-        return dv, da, None, None, None, None, None, None
+        return dv.to(ctx.v_dtype), da, None, None, None, None, None, None
 
 
 class _HardWayLoss(torch.autograd.Function):
@@ -222,7 +248,8 @@ class _HardWayLoss(torch.autograd.Function):
     @staticmethod
     def forward(ctx, v, a, cfg, pos_idx, col_offset, divisor, col_mult=1):
         need_grad = v.requires_grad or a.requires_grad
-        v = v.contiguous().float()
+        ctx.v_dtype = v.dtype
+        v = as_head_input(v, cfg)
         a_hat, rn_a = audio_normalize(a)
         out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=need_grad,
                                col_mult=col_mult)
@@ -238,7 +265,7 @@ class _HardWayLoss(torch.autograd.Function):
         scale = float(gloss) / ctx.divisor
         dv, d_ahat = head_backward_raw(v, a_hat, ctx.cfg, ctx.saved, scale, None, None, ctx.col_offset)
         da = audio_normalize_backward(a_hat, rn_a, d_ahat)
-        return dv, da, None, None, None, None, None
+        return dv.to(ctx.v_dtype), da, None, None, None, None, None
 
 
 def hardway_head(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, col_offset=0,
@@ -284,17 +311,17 @@ def hardway_value_and_grad(v, a, cfg: HeadConfig = HeadConfig(), pos_idx=None, c
     _lib.require_cuda(v, a)
     if v.dim() == 4:
         v = v.flatten(2)
-    v = v.contiguous().float()
+    v = as_head_input(v, cfg)
     divisor = float(divisor or v.shape[0])
     if col_mult > 1 and pos_idx is None:
         pos_idx, _ = tube_positions(v.shape[0], col_mult, v.device, col_offset)
     a_hat, rn_a = audio_normalize(a)
     out = head_forward_raw(v, a_hat, cfg, pos_idx, col_offset, False, for_backward=want_grad,
-                           col_mult=col_mult)
+                           col_mult=col_mult, fuse_grad_scale=(1.0 / divisor) if want_grad else 0.0)
     loss = out["loss_sum"] / divisor
     if not want_grad:
         return loss, None, None
-    dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 1.0 / divisor, None, None, col_offset)
+    dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 0.0, None, None, col_offset, rowgrad_done=True)
     da = audio_normalize_backward(a_hat, rn_a, d_ahat)
     return loss, dv, da
 

@@ -5,11 +5,13 @@ The head's kernels are short (tens to hundreds of microseconds; at 8 GPUs a rank
 sharded, by the latency of three small NCCL collectives.  ``HeadStep`` pre-allocates every
 buffer, captures the whole step once and replays it:
 
-    main stream :  normalise local audio -> all_gather(a_hat) -> prep + similarity + pooling + CE
-                   -> backward (cell gradients, dv, d_ahat) -> reduce_scatter(d_ahat)
-                   -> audio normalise Jacobian
-    side stream :  all_reduce of the loss sum (nothing on the critical path consumes it), forked
-                   after the forward and joined at the end, i.e. hidden under the backward
+    main stream :  normalise local audio -> visual prep pass (needs only the rank's OWN audio rows)
+                   -> [join all_gather] similarity + pooling + CE + row gradients (one row kernel)
+                   -> cell gradients -> d_ahat -> reduce_scatter(d_ahat) -> audio normalise Jacobian
+    side stream :  all_gather(a_hat), issued first and hidden under the prep pass; later the
+                   all_reduce of the loss sum (nothing on the critical path consumes it)
+    dv stream   :  the dv contraction, forked after the cell gradients, so the reduce_scatter of
+                   d_ahat (which needs only the d_ahat kernel) runs under it; joined at the end
 
 Inputs are read from the tensors given at construction (fixed addresses): copy new features into
 ``step.v`` / ``step.a`` (or hand in the backbone's output buffers) and call ``step()``.
@@ -33,11 +35,13 @@ class HeadStep:
     are its exact derivatives."""
 
     def __init__(self, v: torch.Tensor, a: torch.Tensor, cfg: HeadConfig = HeadConfig(), group=None,
-                 sharded: bool | None = None, use_graph: bool = True):
+                 sharded: bool | None = None, use_graph: bool = True, overlap: bool = True):
         _lib.require_cuda(v, a)
         if v.dim() == 4:
             v = v.flatten(2)
-        assert v.is_contiguous() and a.is_contiguous() and v.dtype == torch.float32 and a.dtype == torch.float32
+        assert v.is_contiguous() and a.is_contiguous() and a.dtype == torch.float32
+        assert v.dtype == torch.float32 or (v.dtype in (torch.float16, torch.bfloat16) and cfg.precision == "f16")
+        self.overlap = overlap
         self.v, self.a, self.cfg, self.group = v, a, cfg, group
         self.sharded = dist.is_initialized() and dist.get_world_size(group) > 1 if sharded is None else sharded
         self.world = dist.get_world_size(group) if self.sharded else 1
@@ -46,6 +50,7 @@ class HeadStep:
         self.divisor = float(self.world * v.shape[0])
         self.graph = None
         self.side = torch.cuda.Stream(device=v.device)
+        self.dv_stream = torch.cuda.Stream(device=v.device)
         self._out = None
         if use_graph:
             self._capture()
@@ -53,29 +58,50 @@ class HeadStep:
     # one eager step; also the body that gets captured
     def _body(self):
         v, a, cfg = self.v, self.a, self.cfg
-        a_hat_local, rn_local = audio_normalize(a)
-        if self.sharded:
-            a_hat = torch.empty(self.world * self.b_local, a.shape[1], device=a.device, dtype=torch.float32)
-            dist.all_gather_into_tensor(a_hat, a_hat_local, group=self.group)
-        else:
-            a_hat = a_hat_local
-        col_offset = self.rank * self.b_local
-        out = head_forward_raw(v, a_hat, cfg, None, col_offset, False, for_backward=True)
         main = torch.cuda.current_stream()
+        scale = 1.0 / self.divisor
+        a_hat_local, rn_local = audio_normalize(a)
+        col_offset = self.rank * self.b_local
+        if self.sharded and self.overlap:
+            # all_gather first, on the side stream; the one pass over the visual maps needs only this
+            # rank's own audio rows (its positives) and runs under it
+            n_all = self.world * self.b_local
+            a_hat = torch.empty(n_all, a.shape[1], device=a.device, dtype=torch.float32)
+            self.side.wait_stream(main)
+            with torch.cuda.stream(self.side):
+                dist.all_gather_into_tensor(a_hat, a_hat_local, group=self.group)
+            out = head_forward_raw(v, a_hat_local, cfg, None, 0, False, for_backward=True,
+                                   stages=_lib.STAGE_PREP, n_a_total=n_all)
+            main.wait_stream(self.side)
+            out = head_forward_raw(v, a_hat, cfg, None, col_offset, False, stages=_lib.STAGE_SIM, out=out,
+                                   fuse_grad_scale=scale)
+        else:
+            if self.sharded:
+                a_hat = torch.empty(self.world * self.b_local, a.shape[1], device=a.device, dtype=torch.float32)
+                dist.all_gather_into_tensor(a_hat, a_hat_local, group=self.group)
+            else:
+                a_hat = a_hat_local
+            out = head_forward_raw(v, a_hat, cfg, None, col_offset, False, for_backward=True,
+                                   fuse_grad_scale=scale)
         total = out["loss_sum"]
         if self.sharded:                      # nobody on the critical path needs the loss value
             total = out["loss_sum"].clone()
             self.side.wait_stream(main)
             with torch.cuda.stream(self.side):
                 dist.all_reduce(total, group=self.group)
-        dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 1.0 / self.divisor, None, None, col_offset)
+        ext = self.dv_stream if (self.sharded and self.overlap) else None
+        dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 0.0, None, None, col_offset, rowgrad_done=True,
+                                       dv_stream=ext)
         if self.sharded:
             d_local = torch.empty_like(a_hat_local)
-            dist.reduce_scatter_tensor(d_local, d_ahat, group=self.group)
-            main.wait_stream(self.side)
+            dist.reduce_scatter_tensor(d_local, d_ahat, group=self.group)     # under the dv kernel
         else:
             d_local = d_ahat
         da = audio_normalize_backward(a_hat_local, rn_local, d_local)
+        if self.sharded:
+            main.wait_stream(self.side)
+            if ext is not None:
+                main.wait_stream(ext)
         loss = total / self.divisor
         return loss, dv, da, out
 
@@ -134,12 +160,12 @@ class HostHeadPipeline:
             return dv, da
 
     def __init__(self, v_shape, a_shape, cfg: HeadConfig = HeadConfig(), group=None, device=None,
-                 use_graph: bool = True):
+                 use_graph: bool = True, v_dtype: torch.dtype = torch.float32):
         dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.copy_stream = torch.cuda.Stream(device=dev)
         self.slots = []
         for _ in range(2):
-            v = torch.zeros(*v_shape, device=dev, dtype=torch.float32)
+            v = torch.zeros(*v_shape, device=dev, dtype=v_dtype)    # fp16 / bf16 features: half the H2D bytes
             a = torch.zeros(*a_shape, device=dev, dtype=torch.float32)
             if v.dim() == 4:
                 v = v.flatten(2)

@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg5", choices=["cfg5", "cfg2"])
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--precision", default="f16", choices=["f16", "fp32"])
     ap.add_argument("--no-extras", action="store_true", help="skip eval / cfg2 / train-step extras")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch the step kernel by kernel instead of replaying a CUDA graph")
@@ -290,16 +290,16 @@ def main():
     stage_ms = {k: (ms / n if n else None) for k, (ms, n) in prof.items()}
     sim_ms = stage_ms["sim"]
     local_cells = b_local * b_global * P
-    tensor_bound = b_global >= 512 and args.precision == "bf16"
+    tensor_bound = b_global >= 512 and args.precision == "f16"
     if tensor_bound:
         ach = local_cells * FLOP_FWD_PER_CELL / (sim_ms * 1e-3) / 1e12
-        roofline = {"kernel": "sim_bf16_kernel (avt_head_tc.cu)", "bound": "tensor", "achieved": ach,
+        roofline = {"kernel": "sim_tc_kernel (avt_head_tc.cu)", "bound": "tensor", "achieved": ach,
                     "peak": pk["tc_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tc_sustained"],
                     "traffic": None, "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a step)",
                     "ms_per_launch": sim_ms}
         if world == 1 and args.workload == "cfg5":     # DRAM bytes per launch from the committed ncu --set full capture
             roofline["traffic"] = 206644224 + 13373184
-            roofline["traffic_source"] = "profiles/r1_ncu_head_final.txt (dram__bytes_read + dram__bytes_write, sim_bf16_kernel<0>, same shape)"
+            roofline["traffic_source"] = "profiles/r1_ncu_head_final.txt (dram__bytes_read + dram__bytes_write, sim_tc_kernel<0>, same shape)"
     else:
         bytes_alg = b_local * C * P * 4 + b_global * C * 4 + b_local * (b_global + 2) * 4 + 3 * b_local * P * 4
         tot = (stage_ms["prep"] or 0) + (sim_ms or 0) + (stage_ms["finish"] or 0)
@@ -438,13 +438,14 @@ def extras(avt, ev, _lib, cfg, dev, pk):
     mk = torch.empty(n, 224, 224, dtype=torch.uint8, device=dev)
     iw = torch.empty(n, dtype=torch.int32, device=dev); uw = torch.empty_like(iw)
     ci = torch.empty(n, dtype=torch.float64, device=dev)
+    tkt = torch.empty(64, dtype=torch.uint8, device=dev)
     lib = _lib.load()
 
     def run_eval(materialise=True):
         _lib.check(lib.avt_eval_maps(_lib.ptr(maps), n, _lib.ptr(gt), None, None, 0, 0,
                                      _lib.ptr(up) if materialise else None,
                                      _lib.ptr(mk) if materialise else None, _lib.ptr(iw), _lib.ptr(uw),
-                                     _lib.ptr(ci), _lib.stream_ptr()), "avt_eval_maps")
+                                     _lib.ptr(ci), _lib.ptr(tkt), _lib.stream_ptr()), "avt_eval_maps")
     ms = timed(run_eval, 10, 3)            # 1.56 GB of traffic per launch: larger than L2
     gbs = n * EVAL_BYTES_PER_MAP / (ms * 1e-3) / 1e9
     out["eval_cfg3"] = {"maps_per_s": n / (ms * 1e-3), "ms": ms, "mode": "materialising (dense GT, up224 + mask out)",
@@ -460,7 +461,7 @@ def extras(avt, ev, _lib, cfg, dev, pk):
 
     def run_eval_boxes():
         _lib.check(lib.avt_eval_maps(_lib.ptr(maps), n, None, _lib.ptr(bxs), _lib.ptr(bcs), 2, 0, None, None,
-                                     _lib.ptr(iw), _lib.ptr(uw), _lib.ptr(ci), _lib.stream_ptr()), "avt_eval_maps")
+                                     _lib.ptr(iw), _lib.ptr(uw), _lib.ptr(ci), _lib.ptr(tkt), _lib.stream_ptr()), "avt_eval_maps")
     ms3 = timed(run_eval_boxes, 10, 3)
     out["eval_cfg3_boxes_in_scalars_out"] = {"maps_per_s": n / (ms3 * 1e-3), "ms": ms3}
     # the reference's CPU eval glue (restated, cv2-free) on a bounded sample, single core

@@ -12,7 +12,8 @@
  * Return value: 0 = ok, negative = error (avt_last_error() gives the text, per thread).
  *
  * Layouts
- *   v        [N_v, C, P]  fp32   raw visual maps, NCHW with H*W flattened (P = 196)
+ *   v        [N_v, C, P]  fp32   raw visual maps, NCHW with H*W flattened (P = 196); fp16 / bf16
+ *                                accepted by the tensor-core path (v_dtype = AVT_DTYPE_*)
  *   a / a_hat[N_a, C]     fp32   pooled audio embeddings, raw / L2-normalised
  *   pos_idx  [N_v]        int32  column of a_hat that is row n's positive, or NULL
  *                                for pos[n] = col_offset + n (model.py:115 has
@@ -40,6 +41,12 @@ extern "C" {
 #define AVT_PRECISION_F16      1   /* tcgen05 kind::f16: IEEE fp16 operands (11-bit significand; the
                                       operands are L2-normalised, the cell gradients carry a
                                       power-of-two scale), fp32 accumulate in tensor memory */
+
+/* element type of the visual maps handed to the head: fp32 as the reference's fp32 backbones emit
+ * them, or fp16 / bf16 when the backbone ran under autocast (AVT_PRECISION_F16 only) */
+#define AVT_DTYPE_F32          0
+#define AVT_DTYPE_F16          1
+#define AVT_DTYPE_BF16         2
 
 /* ground-truth rasterisation modes (utils.py:241-309) */
 #define AVT_GT_VGGSS           0   /* union of boxes            -> weights {0,1},   den 1 */
@@ -111,7 +118,20 @@ int avt_audio_normalize_backward(const float* a_hat, const float* rnorm_a,
  * 1/T of the similarity flops, 1/T of the audio-backbone work upstream. */
 size_t avt_head_workspace_bytes(int N_v, int N_a, int C, int P, int precision, int backward);
 
-int avt_head_forward(const float* v, const float* a_hat,
+/* stages of avt_head_forward (0 = both).  AVT_STAGE_PREP is the one pass over the visual maps
+ * (1/||v||, the positive map A, mean_c, the fp16 operand copy); it reads a_hat ONLY at the rows'
+ * positives, so a row-sharded caller may run it with just its own audio rows (N_a = rows held,
+ * col_offset = 0) while the all-gather of the other ranks' rows is still in flight, then call
+ * AVT_STAGE_SIM (audio operand, contraction, pooling, row finish) with the full a_hat.
+ * fuse_grad_scale != 0 (with AVT_STAGE_SIM; needs a backward-sized workspace): the fused training
+ * step -- the row-finish kernel also emits the row gradients of  fuse_grad_scale * sum_n loss_rows[n],
+ * and avt_head_backward is then called with AVT_BWD_ROWGRAD_DONE (one launch less on the
+ * critical path; dloss_scale / dlogits / dA / dWeighted / dloss_rows must be 0 / NULL). */
+#define AVT_STAGE_PREP         1
+#define AVT_STAGE_SIM          2
+#define AVT_BWD_ROWGRAD_DONE   1
+
+int avt_head_forward(const void* v, int v_dtype, const float* a_hat,
                      int N_v, int N_a, int C, int P,
                      const int32_t* pos_idx, int col_offset,
                      float eps, float eps2, float tau, float temp, float mask_scale,
@@ -119,6 +139,7 @@ int avt_head_forward(const float* v, const float* a_hat,
                      float* A, float* Pos, float* Neg, float* logits,
                      float* loss_rows, float* loss_sum, float* weighted_A,
                      float* rnorm_v, float* sim, float* den,
+                     int stages, float fuse_grad_scale,
                      void* workspace, size_t workspace_bytes, void* stream);
 
 /* Backward of the head (autograd of model.py:117-146 + CrossEntropyLoss).
@@ -130,8 +151,12 @@ int avt_head_forward(const float* v, const float* a_hat,
  * ran with, which still holds mean_c v_hat).  Writes dv [N_v, C, P] (gradient wrt the RAW maps) and
  * d_ahat [N_a, C] (gradient wrt the NORMALISED audio rows, summed over this call's
  * N_v rows; finish with avt_audio_normalize_backward, after a reduce-scatter when
- * rows are sharded over ranks). */
-int avt_head_backward(const float* v, const float* a_hat,
+ * rows are sharded over ranks).
+ * dv_stream (cudaStream_t or NULL): when given, the dv contraction is enqueued on THAT stream
+ * (ordered after the stages it depends on) and d_ahat completes on `stream` without waiting for
+ * it -- a sharded caller starts its reduce-scatter of d_ahat under the dv kernel and orders
+ * dv_stream before whatever consumes dv.  NULL: everything is complete in `stream` order. */
+int avt_head_backward(const void* v, int v_dtype, const float* a_hat,
                       int N_v, int N_a, int C, int P,
                       const int32_t* pos_idx, int col_offset,
                       float eps, float eps2, float tau, float temp, float mask_scale,
@@ -142,6 +167,7 @@ int avt_head_backward(const float* v, const float* a_hat,
                       const float* dlogits, const float* dA,
                       const float* dWeighted,
                       float* dv, float* d_ahat,
+                      int flags, void* dv_stream,
                       void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- evaluation -------------------------------------------------------------------

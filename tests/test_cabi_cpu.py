@@ -36,9 +36,9 @@ def test_library_exports_every_declared_symbol(lib):
 def test_version_and_error_paths_without_gpu(lib):
     assert lib.avt_version() >= 100
     # argument validation happens before any CUDA call: bad shapes report AVT_ERR_INVALID
-    rc = lib.avt_head_forward(None, None, 0, 0, 512, 196, None, 0, 0.65, 0.4, 0.03, 0.07, 100.0,
+    rc = lib.avt_head_forward(None, 0, None, 0, 0, 512, 196, None, 0, 0.65, 0.4, 0.03, 0.07, 100.0,
                               1, 1, 0, 1, None, None, None, None, None, None, None, None, None, None,
-                              None, ctypes.c_size_t(0), None)
+                              0, 0.0, None, ctypes.c_size_t(0), None)
     assert rc == -1 and b"N_v" in lib.avt_last_error()
     assert lib.avt_head_workspace_bytes(128, 128, 512, 196, 1, 1) > 128 * 196 * 512 * 2
     assert lib.avt_head_workspace_bytes(128, 128, 512, 196, 0, 0) < 1 << 20

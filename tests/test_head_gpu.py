@@ -522,3 +522,60 @@ def test_two_host_threads_one_device():
     th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
     [t.start() for t in th]; [t.join() for t in th]
     assert not bad
+
+
+def test_fused_row_gradients_equal_separate_kernel():
+    """The fused training step (row gradients out of finish_rows_kernel, AVT_BWD_ROWGRAD_DONE) gives
+    the bits of the two-kernel path (row_grad_kernel after the forward), tube mode included."""
+    from audio_visual_tubes_b200 import HeadConfig, hardway_loss, hardway_value_and_grad
+    for prec in PRECISIONS:
+        for (nv, na, t) in [(40, 40, 1), (48, 6, 8), (130, 130, 1)]:
+            v, a = head_features(nv, na, 5 + nv, "mix")
+            cfg = HeadConfig(precision=prec)
+            vt = torch.tensor(v, device="cuda", requires_grad=True)
+            at = torch.tensor(a, device="cuda", requires_grad=True)
+            loss = hardway_loss(vt, at, cfg, col_mult=t)                  # autograd: separate row_grad_kernel
+            loss.backward()
+            l2, dv2, da2 = hardway_value_and_grad(vt.detach(), at.detach(), cfg, col_mult=t)   # fused
+            assert float(loss) == float(l2[0])
+            if prec == "f16":
+                assert torch.equal(vt.grad, dv2)
+            else:
+                assert relnorm(dv2.cpu().numpy(), vt.grad.cpu().numpy()) < 1e-6
+            assert relnorm(da2.cpu().numpy(), at.grad.cpu().numpy()) < 1e-5   # d_ahat: atomics order
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_half_precision_feature_maps(dtype):
+    """fp16 / bf16 visual maps (a backbone under autocast; half the H2D bytes of the host pipeline)
+    give exactly what the fp32 entry gives on the same rounded values, and gradients flow back in
+    the maps' dtype."""
+    from audio_visual_tubes_b200 import HeadConfig, hardway_head, hardway_value_and_grad
+    v, a = head_features(24, 24, 19, "mix")
+    cfg = HeadConfig(precision="f16")
+    vh = torch.tensor(v, device="cuda").to(dtype)
+    at = torch.tensor(a, device="cuda")
+    l_h, dv_h, da_h = hardway_value_and_grad(vh, at, cfg)
+    l_f, dv_f, da_f = hardway_value_and_grad(vh.float(), at, cfg)
+    assert float(l_h[0]) == float(l_f[0]) and torch.equal(dv_h, dv_f) and dv_h.dtype == torch.float32
+    vg = vh.clone().requires_grad_(True)
+    out = hardway_head(vg, at, cfg)
+    out[5].mean().backward()
+    assert vg.grad.dtype == dtype
+    # the CUDA-core fp32 path takes them too, by an explicit up-cast on the host side
+    lg32 = hardway_head(vh, at, HeadConfig(precision="fp32"))[1]
+    assert rel(out[1].detach().cpu().numpy(), lg32.cpu().numpy()) < 2e-3
+
+
+def test_head_step_graph_equals_eager():
+    from audio_visual_tubes_b200 import HeadConfig, HeadStep, hardway_value_and_grad
+    v, a = head_features(96, 96, 23, "mix")
+    vt = torch.tensor(v, device="cuda"); at = torch.tensor(a, device="cuda")
+    cfg = HeadConfig(precision="f16")
+    l0, dv0, da0 = hardway_value_and_grad(vt, at, cfg)
+    hs = HeadStep(vt, at, cfg)
+    hs()
+    l1, dv1, da1 = hs()
+    torch.cuda.synchronize()
+    assert float(l0[0]) == float(l1[0]) and torch.equal(dv0, dv1)
+    assert relnorm(da1.cpu().numpy(), da0.cpu().numpy()) < 1e-5
