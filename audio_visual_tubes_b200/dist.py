@@ -51,7 +51,8 @@ class _ShardedHardWayLoss(torch.autograd.Function):
         if v.shape[0] != b_local:
             raise RuntimeError("sharded head: every rank needs as many visual maps as audio rows")
         need_grad = v.requires_grad or a.requires_grad
-        v = v.contiguous().float()
+        ctx.v_dtype = v.dtype
+        v = as_head_input(v, cfg)
         a_hat_local, rn_local = normalize(a.contiguous().float())
         a_hat = torch.empty(world * b_local, a.shape[1], device=a.device, dtype=torch.float32)
         dist.all_gather_into_tensor(a_hat, a_hat_local.contiguous(), group=group)
@@ -74,7 +75,7 @@ class _ShardedHardWayLoss(torch.autograd.Function):
         d_local = torch.empty_like(a_hat_local)
         dist.reduce_scatter_tensor(d_local, d_ahat.contiguous(), group=ctx.group)
         da = normalize_backward(a_hat_local, rn_local, d_local)
-        return dv, da, None, None, None
+        return dv.to(ctx.v_dtype), da, None, None, None
 
 
 def sharded_hardway_loss(v, a, cfg: HeadConfig = HeadConfig(), group=None, compute=None):

@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--no-extras", action="store_true", help="skip eval / cfg2 / train-step extras")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch the step kernel by kernel instead of replaying a CUDA graph")
+    ap.add_argument("--no-overlap", action="store_true", help="sharded step without the all-gather / reduce-scatter overlap (A/B)")
     return ap.parse_args()
 
 
@@ -131,53 +132,85 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU baseline
-def cpu_head_baseline(b_global, rows, steps, warmup, seed=1234):
-    """The reference's own arithmetic for the head (eager fp32 torch ops with the A0-sized
-    temporaries, model.py:117-146 + CrossEntropyLoss + backward) on the host cores, for a
-    block of `rows` visual rows against all b_global audio columns."""
+def workload_string(name, b_local, b_global):
+    return (f"{name}: head fwd+bwd, global B={b_global} ({b_local} visual rows/rank x {b_global} audio), "
+            f"C=512, P=196, features |randn| fp32 NCHW")
+
+
+def cpu_head_baseline(b_sample, steps, warmup, seed=1234):
+    """The reference's own head on the host cores: the UNMODIFIED ``AVENet.forward`` (model.py:112-154,
+    from oracle/_ref, backbones swapped for nn.Identity so that features are the inputs) +
+    ``nn.CrossEntropyLoss`` + ``backward()`` exactly as train_hardway_1frame.py:129-133 chains them,
+    eager fp32 torch on all host cores.  The reference can only score SQUARE batches (its mask is
+    B x B, model.py:115) and materialises ~10 A0-sized fp32 temporaries (8 GB at B=1024), so the
+    timed sample is a square batch of ``b_sample`` clips; cells/s is what is compared.  Falls back
+    to the oracle port (same torch ops, restated) when oracle/_ref did not travel."""
     import numpy as np
     import torch
-    from oracle import head_oracle as ho
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     g = torch.Generator().manual_seed(seed)
-    v = torch.randn(rows, C, P, generator=g).abs_()
-    a = torch.randn(b_global, C, generator=g).abs_()
+    v = torch.randn(b_sample, C, 14, 14, generator=g).abs_()
+    a = torch.randn(b_sample, C, 1, 1, generator=g).abs_()
+    kind = "port"
+    try:
+        from oracle import make_ref
+        if make_ref.available():
+            net = make_ref.reference_head()
+            crit = torch.nn.CrossEntropyLoss()
+            tgt = torch.zeros(b_sample).long()
+
+            def one():
+                vt = v.clone().requires_grad_(True)
+                at = a.clone().requires_grad_(True)
+                out = net(vt, at)
+                loss = crit(out[1], tgt)
+                loss.backward()
+                return float(loss.detach())
+            kind = "reference"
+    except Exception as e:                                   # noqa: BLE001
+        sys.stderr.write(f"[bench] oracle/_ref unusable ({e!r}); timing the oracle port instead\n")
+    if kind == "port":
+        from oracle import head_oracle as ho
+
+        def one():
+            return ho.reference_style_forward_torch(v.flatten(2), a.view(b_sample, C), backward=True)
     for _ in range(warmup):
-        ho.reference_style_rows_torch(v, a, 0, backward=True)
+        one()
     ts = []
     for _ in range(steps):
         t0 = time.perf_counter()
-        ho.reference_style_rows_torch(v, a, 0, backward=True)
+        one()
         ts.append(time.perf_counter() - t0)
     t = float(np.median(ts))
-    cells = rows * b_global * P
-    return dict(value=cells / t, unit=UNIT, cores=cores, kind="port",
-                sample=f"{rows} of {b_global} visual rows x {b_global} audio columns, fwd+bwd, "
-                       f"median of {steps} after {warmup} warm-up; eager fp32 torch port of "
-                       f"model.py:117-146 (oracle/head_oracle.py)",
+    cells = b_sample * b_sample * P
+    what = ("the UNMODIFIED reference AVENet.forward (oracle/_ref, Identity backbones) + CrossEntropyLoss + backward"
+            if kind == "reference" else "eager fp32 torch port of model.py:117-146 (oracle/head_oracle.py) + CE + backward")
+    return dict(value=cells / t, unit=UNIT, cores=cores, kind=kind,
+                sample=f"square batch of {b_sample} clips ({cells} cells) per step, fwd+bwd, median of {steps} "
+                       f"after {warmup} warm-up; {what}; eager fp32 on {cores} host threads",
                 seconds_per_sample=t), t
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path (the oracle port; the
-    reference is pure Python and cannot travel to this box) on all host cores."""
+    """--impl reference: the reference's own CPU implementation of the path on all host cores,
+    same metric / unit / config string / steps / warm-up as the GPU arm; each step is a bounded
+    sample (a square batch of 256 clips) of the workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     world = args.gpus
     b_local, b_global, scaling = workload_shape(args.workload, world)
-    rows = min(64, b_global)
-    steps = max(1, min(args.steps, 5))
-    warm = max(1, min(args.warmup, 2))
-    base, t = cpu_head_baseline(b_global, rows, steps, warm)
+    b_sample = min(256, b_global)
+    base, t = cpu_head_baseline(b_sample, args.steps, args.warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT,
-        "n_gpus": world, "steps": steps, "warmup": warm, "ms_per_step": t * 1e3,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3,
         "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"{args.workload}: head fwd+bwd, B={b_global}, C=512, P=196 "
-                               f"(bounded sample: {rows} rows per step)"},
+        "config": {"workload": workload_string(args.workload, b_local, b_global),
+                   "sample": f"each step = a square batch of {b_sample} clips on the host cores "
+                             f"(the reference's B x B mask admits no row block; full B=1024 needs ~8 GB of temporaries)"},
         "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -213,10 +246,17 @@ def main():
     pk = peaks()
     cfg = avt.HeadConfig(precision=args.precision)
 
+    # ONE seeded GLOBAL batch, sliced by rank: the loss at N ranks is the loss at 1 (checked below)
     b_local, b_global, scaling = workload_shape(args.workload, world)
-    g = torch.Generator(device=dev).manual_seed(1234 + rank)
-    v = torch.randn(b_local, C, P, device=dev, generator=g).abs_()       # post-ReLU-like maps
-    a = torch.randn(b_local, C, device=dev, generator=g).abs_()
+    g = torch.Generator(device=dev).manual_seed(1234)
+    v_glob = torch.randn(b_global, C, P, device=dev, generator=g).abs_()      # post-ReLU-like maps
+    a_glob = torch.randn(b_global, C, device=dev, generator=g).abs_()
+    sl = slice(rank * b_local, (rank + 1) * b_local)
+    loss_global_1gpu = float(avt.hardway_value_and_grad(v_glob, a_glob, cfg, want_grad=False)[0][0])
+    v = v_glob[sl].clone()
+    a = a_glob[sl].clone()
+    del v_glob, a_glob
+    torch.cuda.empty_cache()
     cells_per_step = b_global * b_global * P
     in_bytes = v.numel() * 4
     flush = None
@@ -225,7 +265,7 @@ def main():
 
     # the product's fast path: the whole step (incl. the NCCL collectives) captured in a CUDA graph
     from audio_visual_tubes_b200.step import HeadStep
-    hs = HeadStep(v, a, cfg, use_graph=not args.no_graph)
+    hs = HeadStep(v, a, cfg, use_graph=not args.no_graph, overlap=not args.no_overlap)
 
     def step():
         return hs()
@@ -244,7 +284,8 @@ def main():
         step()
     barrier()
 
-    # ---- stage times and launch count: one profiled eager pass (events cannot live in a graph)
+    # ---- stage times and launch count: one profiled eager pass (events cannot live in a graph; with
+    # profiling on the library runs every stage on ONE stream, so each time is that kernel alone)
     _lib.profile_enable(True)
     n0 = _lib.launch_count()
     for _ in range(3):
@@ -285,93 +326,64 @@ def main():
     ms_step = ms_total / args.steps
     value = cells_per_step / (ms_step * 1e-3)
     loss_val = float(loss.cpu()[0])
+    # the same global batch on 1 GPU and on N: same loss (sum order differs only)
+    assert abs(loss_val - loss_global_1gpu) <= 2e-6 * max(1.0, abs(loss_global_1gpu)), (loss_val, loss_global_1gpu)
 
-    # ---- roofline of the dominant kernel (the forward contraction + pooling epilogue)
+    # ---- rooflines.  Event-timed kernels inside a millisecond-long step run at burst clocks, so the
+    # burst bf16 / fp16 tensor peak is the denominator; per kernel and for the whole step.
     stage_ms = {k: (ms / n if n else None) for k, (ms, n) in prof.items()}
-    sim_ms = stage_ms["sim"]
     local_cells = b_local * b_global * P
+    gflop = local_cells * FLOP_FWD_PER_CELL / 1e9            # one contraction = 2*C flop per cell
     tensor_bound = b_global >= 512 and args.precision == "f16"
-    if tensor_bound:
-        ach = local_cells * FLOP_FWD_PER_CELL / (sim_ms * 1e-3) / 1e12
-        roofline = {"kernel": "sim_tc_kernel (avt_head_tc.cu)", "bound": "tensor", "achieved": ach,
-                    "peak": pk["tc_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tc_sustained"],
-                    "traffic": None, "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a step)",
-                    "ms_per_launch": sim_ms}
-        if world == 1 and args.workload == "cfg5":     # DRAM bytes per launch from the committed ncu --set full capture
-            roofline["traffic"] = 206644224 + 13373184
-            roofline["traffic_source"] = "profiles/r1_ncu_head_final.txt (dram__bytes_read + dram__bytes_write, sim_tc_kernel<0>, same shape)"
+    kern = {}
+    for key, name, credit in (("sim", "sim_tc_kernel<false> (forward contraction + pooling)", 1.0),
+                              ("bwd_g", "sim_tc_kernel<true> (recompute + cell gradients)", 0.0),
+                              ("bwd_dv", "bwd_dv_pair_kernel (dv contraction + normalise Jacobian)", 1.0),
+                              ("bwd_da", "bwd_da_pair_kernel (d_ahat contraction)", 1.0)):
+        ms = stage_ms.get(key)
+        if ms:
+            tf = gflop / ms                                   # GFLOP / ms = TFLOP/s of tensor work EXECUTED
+            kern[key] = {"kernel": name, "ms": ms, "executed_tflops": tf, "frac_of_burst_peak": tf / pk["tc_burst"],
+                         "algorithmic_credit": credit}
+    step_tflops = cells_per_step * (FLOP_FWD_PER_CELL + FLOP_BWD_PER_CELL) / (ms_step * 1e-3) / 1e12 / world
+    if tensor_bound and kern:
+        top = max(kern, key=lambda k: kern[k]["ms"])
+        roofline = {"kernel": kern[top]["kernel"], "bound": "tensor", "achieved": kern[top]["executed_tflops"],
+                    "peak": pk["tc_burst"], "unit": "TFLOP/s", "frac": kern[top]["frac_of_burst_peak"],
+                    "traffic": None, "ms_per_launch": kern[top]["ms"],
+                    "peak_source": pk["source"] + ", BURST fp16/bf16 dense (kernel event-timed inside a ~1 ms step)",
+                    "note": "the longest kernel of the step; 'achieved' counts the MMA flops it executes "
+                            "(the recompute of S in the cell-gradient kernel earns no algorithmic credit: see step_frac)",
+                    "step_frac": step_tflops / pk["tc_burst"], "step_tflops_per_gpu": step_tflops,
+                    "step_frac_of_sustained": step_tflops / pk["tc_sustained"], "kernels": kern}
+        tr = NCU_TRAFFIC.get(top) if (world == 1 and args.workload == "cfg5") else None
+        if tr:
+            roofline["traffic"], roofline["traffic_source"] = tr
     else:
         bytes_alg = b_local * C * P * 4 + b_global * C * 4 + b_local * (b_global + 2) * 4 + 3 * b_local * P * 4
-        tot = (stage_ms["prep"] or 0) + (sim_ms or 0) + (stage_ms["finish"] or 0)
+        tot = (stage_ms["prep"] or 0) + (stage_ms["sim"] or 0) + (stage_ms["finish"] or 0)
         ach = bytes_alg / (tot * 1e-3) / 1e9
         roofline = {"kernel": "head forward (prep + sim + finish)", "bound": "hbm", "achieved": ach,
                     "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"], "traffic": None,
-                    "peak_source": pk["source"], "ms_per_launch": tot}
+                    "peak_source": pk["source"], "ms_per_launch": tot, "kernels": kern}
 
     # ---- e2e: the same step from HOST buffers (pinned), H2D inside the timed region, loss D2H.
-    # The product's host-facing call is HostHeadPipeline (step.py): every step copies its own
-    # features host->device and reads its own loss back; the copy of step i+1 runs on a copy stream
-    # under the compute of step i.  The serial variant (copy, compute, read, one after another on
-    # one stream) is timed beside it.
-    e2e_steps = max(4, min(args.steps, 10))
-    vh = v.cpu().pin_memory()
-    ah = a.cpu().pin_memory()
+    e2e = e2e_leg(args, avt, cfg, hs, v, a, dev, world, barrier, loss_val, cells_per_step)
 
-    def e2e_serial_step():
-        v.copy_(vh, non_blocking=True)            # H2D of this step's features (pinned source)
-        a.copy_(ah, non_blocking=True)
-        l, _, _ = hs()
-        return float(l.cpu()[0])                  # D2H of the loss
-
-    def timed(fn_loop):
-        barrier()
-        t0 = time.perf_counter()
-        fn_loop()
-        barrier()
-        te = torch.tensor([(time.perf_counter() - t0) / e2e_steps], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        return float(te[0])
-
-    for _ in range(2):
-        e2e_serial_step()
-    t_serial = timed(lambda: [e2e_serial_step() for _ in range(e2e_steps)])
-
-    from audio_visual_tubes_b200.step import HostHeadPipeline
-    pipe = HostHeadPipeline(tuple(v.shape), tuple(a.shape), cfg, use_graph=not args.no_graph)
-    e2e_losses = []
-
-    def e2e_pipelined(n):
-        pend = None
-        for _ in range(n):
-            h = pipe.submit(vh, ah)               # H2D of this step + compute, asynchronous
-            if pend is not None:
-                e2e_losses.append(pend.loss())    # D2H read of the previous step's loss
-            pend = h
-        e2e_losses.append(pend.loss())
-
-    e2e_pipelined(3)
-    e2e_losses.clear()
-    t_pipe = timed(lambda: e2e_pipelined(e2e_steps))
-    assert len(e2e_losses) == e2e_steps and all(abs(x - loss_val) <= 1e-5 * max(1.0, abs(loss_val)) for x in e2e_losses), \
-        (e2e_losses, loss_val)
-    e2e = {"value": cells_per_step / t_pipe, "unit": UNIT,
-           "h2d_bytes_per_step": (vh.numel() + ah.numel()) * 4, "d2h_bytes_per_step": 4,
-           "ms_per_step": t_pipe * 1e3, "steps": e2e_steps,
-           "path": "HostHeadPipeline.submit (double-buffered: H2D of step i+1 under compute of step i)",
-           "h2d_GBps": (vh.numel() + ah.numel()) * 4 / t_pipe / 1e9,
-           "serial_ms_per_step": t_serial * 1e3, "serial_value": cells_per_step / t_serial}
-    del pipe
-    del vh, ah
-
-    # ---- extras: evaluation kernel (config 3), B = 128 step (config 2), whole train step
+    # ---- extras.  Collective ones (train clips/s with DDP backbones, sharded eval) run on every rank;
+    # the single-GPU ones on rank 0 only.
     also = {}
-    if rank == 0 and not args.no_extras:
-        also.update(extras(avt, ev, _lib, cfg, dev, pk))
+    if not args.no_extras:
+        try:
+            also.update(extras_collective(avt, ev, _lib, cfg, dev, world, rank, barrier))
+        except Exception as e:                               # noqa: BLE001  keep the headline line alive
+            also["collective_error"] = repr(e)[:300]
+        if rank == 0 and world == 1:
+            also.update(extras(avt, ev, _lib, cfg, dev, pk))
 
     cpu_base = None
-    if rank == 0 and not args.no_cpu_baseline:
-        cpu_base, _ = cpu_head_baseline(b_global, min(64, b_global), 3, 1)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_base, _ = cpu_head_baseline(min(256, b_global), 3, 1)
         cpu_base = {k: cpu_base[k] for k in ("value", "unit", "cores", "kind", "sample")}
 
     if rank == 0:
@@ -379,18 +391,18 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": scaling, "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-            "config": {"workload": f"{args.workload}: head fwd+bwd, global B={b_global} "
-                                   f"({b_local} visual rows/rank x {b_global} audio), C=512, P=196, "
-                                   f"features |randn| fp32 NCHW",
+            "config": {"workload": workload_string(args.workload, b_local, b_global),
                        "parallelism": f"rows sharded over {world} rank(s), NCCL all-gather of audio"
                                       if world > 1 else "single GPU",
                        "launch": "eager" if args.no_graph else "CUDA graph replay (step incl. NCCL captured once)",
+                       "arithmetic": "fp16 operands (tcgen05 kind::f16), fp32 accumulate" if args.precision == "f16"
+                                     else "fp32 CUDA cores",
+                       "batch": "one global batch, seed 1234, sliced by rank",
                        "l2": "inputs (%.0f MB/rank) exceed L2" % (in_bytes / 1e6) if flush is None
                              else "256 MiB L2 flush between timed steps (per-step events)"},
-            "loss": loss_val,
+            "loss": loss_val, "loss_global_batch_on_1_gpu": loss_global_1gpu,
             "roofline": roofline,
             "stage_ms": stage_ms,
-            "fwd_tflops": local_cells * FLOP_FWD_PER_CELL / (sim_ms * 1e-3) / 1e12 if sim_ms else None,
             "cpu_baseline": cpu_base,
             "e2e": e2e,
             "gpu_launches": launches,
@@ -406,6 +418,193 @@ def main():
         dist.barrier()
         torch.cuda.synchronize()
         os._exit(0)
+
+
+# DRAM bytes per launch of the step's kernels from the committed `ncu --set full` capture of this same
+# command (dram__bytes_read.sum + dram__bytes_write.sum); filled from profiles/ by hand after each capture
+NCU_TRAFFIC = {}
+
+
+def e2e_leg(args, avt, cfg, hs, v, a, dev, world, barrier, loss_val, cells_per_step):
+    """The step through the host-facing call, HostHeadPipeline.submit (step.py): every step copies its
+    own features host->device from pinned memory and reads its own loss back; the copy of step i+1
+    runs on a copy stream under the compute of step i.  Timed with fp16 host features (what a
+    backbone under autocast hands over: half the PCIe bytes -- the headline) and with fp32 ones;
+    the serial copy -> compute -> read variant beside them."""
+    import torch
+    import torch.distributed as dist
+    from audio_visual_tubes_b200.step import HostHeadPipeline
+    e2e_steps = max(4, min(args.steps, 10))
+
+    def timed(fn_loop):
+        barrier()
+        t0 = time.perf_counter()
+        fn_loop()
+        barrier()
+        te = torch.tensor([(time.perf_counter() - t0) / e2e_steps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        return float(te[0])
+
+    ah = a.cpu().pin_memory()
+    out = {}
+    for tag, dt in (("f16_features", torch.float16), ("f32_features", torch.float32)):
+        if dt != torch.float32 and args.precision != "f16":
+            continue
+        vh = v.to(dt).cpu().pin_memory()
+        pipe = HostHeadPipeline(tuple(v.shape), tuple(a.shape), cfg, use_graph=not args.no_graph, v_dtype=dt)
+        losses = []
+
+        def pipelined(n):
+            pend = None
+            for _ in range(n):
+                h = pipe.submit(vh, ah)               # H2D of this step + compute, asynchronous
+                if pend is not None:
+                    losses.append(pend.loss())        # D2H read of the previous step's loss
+                pend = h
+            losses.append(pend.loss())
+
+        pipelined(3)
+        losses.clear()
+        t_pipe = timed(lambda: pipelined(e2e_steps))
+        tol = 1e-5 if dt == torch.float32 else 2e-4           # fp16 maps: one more 2^-11 rounding of v
+        assert len(losses) == e2e_steps and all(abs(x - loss_val) <= tol * max(1.0, abs(loss_val)) for x in losses), \
+            (tag, losses, loss_val)
+        nbytes = vh.numel() * vh.element_size() + ah.numel() * 4
+        out[tag] = {"value": cells_per_step / t_pipe, "ms_per_step": t_pipe * 1e3, "h2d_bytes_per_step": nbytes,
+                    "h2d_GBps": nbytes / t_pipe / 1e9, "loss": losses[-1]}
+        del pipe, vh
+    # serial: copy, compute, read, one after another on one stream (fp32 features)
+    vh = v.cpu().pin_memory()
+
+    def serial_step():
+        v.copy_(vh, non_blocking=True)
+        a.copy_(ah, non_blocking=True)
+        l, _, _ = hs()
+        return float(l.cpu()[0])
+    for _ in range(2):
+        serial_step()
+    t_serial = timed(lambda: [serial_step() for _ in range(e2e_steps)])
+    head = out.get("f16_features") or out["f32_features"]
+    e2e = {"value": head["value"], "unit": UNIT, "h2d_bytes_per_step": head["h2d_bytes_per_step"],
+           "d2h_bytes_per_step": 4, "ms_per_step": head["ms_per_step"], "steps": e2e_steps,
+           "h2d_GBps": head["h2d_GBps"],
+           "path": "HostHeadPipeline.submit (double-buffered: H2D of step i+1 under compute of step i), "
+                   + ("fp16 host features" if "f16_features" in out else "fp32 host features")
+                   + "; dv stays on the device for the backbone's backward, the loss (4 B) is read back every step",
+           "variants": out, "serial_fp32_ms_per_step": t_serial * 1e3}
+    return e2e
+
+
+# ----------------------------------------------------------------------------- CPU eval baseline
+_EV = {}
+
+
+def _ref_eval_init(n_maps):
+    """Worker initialiser: the seeded config-3 maps, the real VGG-SS boxes and the reference's utils
+    (oracle/_ref when it travelled -> kind 'reference'; else the numpy oracle -> kind 'port')."""
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    from oracle import eval_oracle as eo
+    g = np.load(os.path.join(ROOT, "tests", "golden", "vggss_golden.npz"))
+    _EV["maps"] = eo.synthetic_maps(n_maps, 0)
+    _EV["boxes"] = [g["boxes"][i, :g["count"][i]].tolist() for i in range(n_maps)]
+    _EV["eo"] = eo
+    _EV["kind"] = "port"
+    try:
+        import cv2                                            # noqa: F401
+        from oracle import make_ref
+        if make_ref.available():
+            _EV["utils"] = make_ref.load()[1]
+            _EV["kind"] = "reference"
+    except Exception:                                         # noqa: BLE001
+        pass
+    return _EV["kind"]
+
+
+def _ref_eval_range(lo_hi):
+    """train_hardway_1frame.py:198-207 for maps lo..hi-1, one Python iteration per clip as the
+    reference runs it: real cv2.resize + the reference's normalize_img / testset_gt / Evaluator."""
+    import types
+    import numpy as np
+    lo, hi = lo_hi
+    out = []
+    if _EV["kind"] == "reference":
+        import cv2
+        U = _EV["utils"]
+        args = types.SimpleNamespace(testset="vggss", gt_all={str(i): _EV["boxes"][i] for i in range(lo, hi)})
+        for i in range(lo, hi):
+            heatmap_now = cv2.resize(_EV["maps"][i], dsize=(224, 224), interpolation=cv2.INTER_LINEAR)
+            heatmap_now = U.normalize_img(-heatmap_now)
+            gt_map = U.testset_gt(args, str(i) + ".mp4")
+            pred = 1 - heatmap_now
+            threshold = np.sort(pred.flatten())[int(pred.shape[0] * pred.shape[1] / 2)]
+            pred[pred > threshold] = 1
+            pred[pred < 1] = 0
+            with np.errstate(divide="ignore", invalid="ignore"):
+                ciou, _, _ = U.Evaluator().cal_CIOU(pred, gt_map, 0.5)
+            out.append(ciou)
+    else:
+        eo = _EV["eo"]
+        for i in range(lo, hi):
+            out.append(eo.evaluate_map(_EV["maps"][i], eo.rasterise_gt(_EV["boxes"][i], "vggss")[0])["ciou"])
+    return out
+
+
+def eval_worker(spec):
+    lo, hi, start_at = spec.split(":")
+    lo, hi, start_at = int(lo), int(hi), float(start_at)
+    kind = _ref_eval_init(hi)
+    _ref_eval_range((lo, lo + 4))
+    late = time.time() > start_at
+    while time.time() < start_at:
+        time.sleep(0.005)
+    t0 = time.time()
+    _ref_eval_range((lo, hi))
+    print(json.dumps({"t0": t0, "t1": time.time(), "late": late, "kind": kind}))
+
+
+def cpu_eval_baseline(n_single=300, per_worker=96):
+    """Reference eval glue on the host cores: single process (as the reference runs it) and one
+    worker process per core."""
+    cores = os.cpu_count() or 1
+    kind = _ref_eval_init(max(n_single, 1))
+    _ref_eval_range((0, 8))
+    t0 = time.perf_counter()
+    _ref_eval_range((0, n_single))
+    t1 = time.perf_counter() - t0
+    res = {"single_process": {"maps_per_s": n_single / t1, "cores": 1, "kind": kind,
+                              "sample": f"{n_single} of the 5158 config-3 maps with their real VGG-SS boxes, "
+                                        "train_hardway_1frame.py:198-207 per clip (cv2.resize, "
+                                        + ("the reference's utils.normalize_img / testset_gt / Evaluator from oracle/_ref)"
+                                           if kind == "reference" else "oracle/eval_oracle.py port)")}}
+    # all cores: one worker PROCESS per core (the multiprocessing.Pool variant of SURVEY 8d, written with
+    # plain subprocesses + a common start time so that no fork happens under a live CUDA context and a
+    # stuck worker is killed by a timeout instead of hanging the bench)
+    try:
+        import subprocess
+        nw = min(cores, 32)
+        start_at = time.time() + 40.0                         # workers import cv2 / torch / sklearn first
+        procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--eval-worker",
+                                   f"{i * per_worker}:{(i + 1) * per_worker}:{start_at}"],
+                                  stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 for i in range(nw)]
+        durs = []
+        for p in procs:
+            try:
+                o, _ = p.communicate(timeout=150)
+                durs.append(json.loads(o.strip().splitlines()[-1]))
+            except Exception:                                 # noqa: BLE001
+                p.kill()
+        if len(durs) == nw and all(d["late"] is False for d in durs):
+            t_end = max(d["t1"] for d in durs); t_beg = min(d["t0"] for d in durs)
+            res["pool_all_cores"] = {"maps_per_s": nw * per_worker / (t_end - t_beg), "cores": nw, "kind": durs[0]["kind"],
+                                     "sample": f"{nw} worker processes x {per_worker} maps each, started together"}
+        else:
+            res["pool_all_cores"] = {"error": f"{len(durs)}/{nw} workers reported in time"}
+    except Exception as e:                                    # noqa: BLE001
+        res["pool_all_cores"] = {"error": repr(e)[:200]}
+    return res
 
 
 def extras(avt, ev, _lib, cfg, dev, pk):
@@ -429,11 +628,13 @@ def extras(avt, ev, _lib, cfg, dev, pk):
         return tot / n
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    # config 3: 5158 maps, materialising mode (dense GT in, up224 + mask out) -- HBM roofline
+    # config 3: 5158 maps against the REAL VGG-SS box lists (tests/golden/vggss_golden.npz: data copied
+    # from metadata/vggss.json), materialising mode (dense GT in, up224 + mask out) -- HBM roofline
     n = 5158
     maps = torch.tensor(eo.synthetic_maps(n, 0), device=dev)
-    gt = torch.zeros(n, 224, 224, dtype=torch.uint8, device=dev)
-    gt[:, 40:160, 50:180] = 1
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "vggss_golden.npz"))
+    real_boxes = [gold["boxes"][i, :gold["count"][i]].tolist() for i in range(n)]
+    gt = avt.rasterise_gt(real_boxes, "vggss").contiguous()            # utils.py:264-273 on the device
     up = torch.empty(n, 224, 224, device=dev)
     mk = torch.empty(n, 224, 224, dtype=torch.uint8, device=dev)
     iw = torch.empty(n, dtype=torch.int32, device=dev); uw = torch.empty_like(iw)
@@ -448,6 +649,12 @@ def extras(avt, ev, _lib, cfg, dev, pk):
                                      _lib.ptr(ci), _lib.ptr(tkt), _lib.stream_ptr()), "avt_eval_maps")
     ms = timed(run_eval, 10, 3)            # 1.56 GB of traffic per launch: larger than L2
     gbs = n * EVAL_BYTES_PER_MAP / (ms * 1e-3) / 1e9
+    # end-to-end numbers of the same maps: must equal what the unmodified reference scored (1e-3)
+    res3 = avt.evaluate_maps(maps, boxes=real_boxes, gt_mode="vggss")
+    out["eval_cfg3_result"] = {"auc": res3["auc"], "ciou_at_half": res3["ciou_at_half"],
+                               "reference_auc": float(gold["auc"]), "reference_ciou_at_half": float(gold["ciou_at_half"]),
+                               "boxes": "real VGG-SS (5158 clips, 12 with negative coordinates, 2 with empty GT)"}
+    assert abs(res3["auc"] - float(gold["auc"])) < 1e-3 and abs(res3["ciou_at_half"] - float(gold["ciou_at_half"])) < 1e-3
     out["eval_cfg3"] = {"maps_per_s": n / (ms * 1e-3), "ms": ms, "mode": "materialising (dense GT, up224 + mask out)",
                         "roofline": {"kernel": "eval_maps_kernel<true>", "bound": "hbm", "achieved": gbs,
                                      "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
@@ -456,22 +663,21 @@ def extras(avt, ev, _lib, cfg, dev, pk):
     out["eval_cfg3_metrics_only"] = {"maps_per_s": n / (ms2 * 1e-3), "ms": ms2}
     # the pipeline mode of the reference's test loop: boxes in (utils.py:264-273 rasterised inside
     # the kernel as bit planes), scalars out -- nothing but 784 B + a few boxes read per clip
-    bxs = torch.tensor([[[50, 40, 180, 160], [10, 100, 90, 200]]], dtype=torch.int16, device=dev).repeat(n, 1, 1).contiguous()
-    bcs = torch.full((n,), 2, dtype=torch.uint8, device=dev)
+    bx_np, bc_np = ev.pack_boxes(real_boxes, "vggss")
+    bxs = torch.as_tensor(bx_np, device=dev).contiguous()
+    bcs = torch.as_tensor(bc_np, device=dev).contiguous()
+    max_b = int(bxs.shape[1])
 
     def run_eval_boxes():
-        _lib.check(lib.avt_eval_maps(_lib.ptr(maps), n, None, _lib.ptr(bxs), _lib.ptr(bcs), 2, 0, None, None,
+        _lib.check(lib.avt_eval_maps(_lib.ptr(maps), n, None, _lib.ptr(bxs), _lib.ptr(bcs), max_b, 0, None, None,
                                      _lib.ptr(iw), _lib.ptr(uw), _lib.ptr(ci), _lib.ptr(tkt), _lib.stream_ptr()), "avt_eval_maps")
     ms3 = timed(run_eval_boxes, 10, 3)
     out["eval_cfg3_boxes_in_scalars_out"] = {"maps_per_s": n / (ms3 * 1e-3), "ms": ms3}
-    # the reference's CPU eval glue (restated, cv2-free) on a bounded sample, single core
-    t0 = time.perf_counter()
-    ns = 200
-    m_np = maps[:ns].cpu().numpy(); g_np = gt[0].cpu().numpy()
-    for i in range(ns):
-        eo.evaluate_map(m_np[i], g_np)
-    out["eval_cpu_baseline"] = {"maps_per_s": ns / (time.perf_counter() - t0), "cores": 1, "kind": "port",
-                                "sample": f"{ns} maps, oracle/eval_oracle.py evaluate_map (numpy)"}
+    # the reference's CPU eval glue on the host cores: single process and one process per core
+    try:
+        out["eval_cpu_baseline"] = cpu_eval_baseline()
+    except Exception as e:                                   # noqa: BLE001
+        out["eval_cpu_baseline"] = {"error": repr(e)[:200]}
     del gt, up, mk
 
     # config 2: B = 128 head step on one GPU, L2 flushed between steps
@@ -487,6 +693,17 @@ def extras(avt, ev, _lib, cfg, dev, pk):
     out["head_cfg2_b128"] = {"cells_per_s": cells / (ms * 1e-3), "ms_fwd_bwd": ms, "ms_fwd": fwd_ms,
                              "fwd_hbm_gbs": bytes_alg / (fwd_ms * 1e-3) / 1e9,
                              "fwd_hbm_frac": bytes_alg / (fwd_ms * 1e-3) / 1e9 / pk["hbm"]}
+
+    # the kernel-to-beat on the same box: the reference's eager PyTorch head on this B200
+    try:
+        out["reference_eager_b200"] = reference_eager_gpu(avt, cfg, dev)
+    except Exception as e:                                   # noqa: BLE001
+        out["reference_eager_b200"] = {"error": repr(e)[:300]}
+    # config 1 (BASELINE.json configs[0]): the reference's own AVENet, B = 8, on the host cores
+    try:
+        out["config1_reference_cpu"] = config1_reference_cpu(avt, cfg, dev)
+    except Exception as e:                                   # noqa: BLE001
+        out["config1_reference_cpu"] = {"error": repr(e)[:300]}
 
     # config 4: tube model, b = 64 clips x T = 16 frames = 1024 frames.  Reference-faithful mode scores
     # every frame against the 1024 REPEATED audio rows (train_3D.py:129-130); tube mode scores it
@@ -561,42 +778,254 @@ def extras(avt, ev, _lib, cfg, dev, pk):
     except Exception as e:
         out["spectrogram_b128_16k"] = {"error": repr(e)[:200]}
 
-    # whole training step, config 2: stock-PyTorch backbones + fused head + Adam
-    try:
-        import types
-        args = types.SimpleNamespace(epsilon=0.65, epsilon2=0.4, tri_map=True, Neg=True)
-        torch.manual_seed(0)
-        net = avt.AVENet(args, False, precision=cfg.precision).to(dev).train()
-        opt = torch.optim.Adam(net.parameters(), lr=1e-6, weight_decay=1e-4)
-        img = torch.randn(128, 3, 224, 224, device=dev)
-        spec = torch.randn(128, 1, 257, 300, device=dev)
+    return out
 
+
+def reference_eager_gpu(avt, cfg, dev):
+    """'the bar to beat on the same box is the reference's own eager PyTorch
+    execution'.  The UNMODIFIED reference head (oracle/_ref AVENet, Identity backbones; model.py:112-154)
+    + nn.CrossEntropyLoss + backward, fp32 eager on this GPU (allow_tf32 off, as the reference never
+    enables it), at B = 128 (config 2) and B = 1024 (configs 4/5: A0 is 822 MB, ~10 such temporaries
+    with autograd).  Same features as the product arm; ours is timed beside it on the same tensors."""
+    import torch
+    from oracle import make_ref
+    torch.backends.cuda.matmul.allow_tf32 = False
+    net = make_ref.reference_head().to(dev)
+    crit = torch.nn.CrossEntropyLoss()
+    res = {"kind": "reference (oracle/_ref, unmodified model.py) on cuda, fp32 eager"}
+    for b in (128, 1024):
+        g = torch.Generator(device=dev).manual_seed(1234)
+        v = torch.randn(b, C, P, device=dev, generator=g).abs_()
+        a = torch.randn(b, C, device=dev, generator=g).abs_()
+        tgt = torch.zeros(b, dtype=torch.long, device=dev)
+
+        def ref_step():
+            vt = v.view(b, C, 14, 14).clone().requires_grad_(True)
+            at = a.view(b, C, 1, 1).clone().requires_grad_(True)
+            o = net(vt, at)
+            loss = crit(o[1], tgt)
+            loss.backward()
+            return loss, vt.grad
+
+        def ours_step():
+            return avt.hardway_value_and_grad(v, a, cfg)
+
+        def timed(fn, n, warm):
+            for _ in range(warm):
+                r = fn()
+            torch.cuda.synchronize()
+            ts = []
+            for _ in range(n):
+                s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s0.record(); r = fn(); s1.record()
+                torch.cuda.synchronize()
+                ts.append(s0.elapsed_time(s1))
+            ts.sort()
+            return ts[len(ts) // 2], r
+        torch.cuda.reset_peak_memory_stats(dev)
+        m0 = torch.cuda.memory_allocated(dev)
+        ms_ref, (l_ref, dv_ref) = timed(ref_step, 5, 2)
+        peak = torch.cuda.max_memory_allocated(dev) - m0
+        ms_ours, (l_ours, dv_ours, _) = timed(ours_step, 10, 3)
+        cells = b * b * P
+        err = float((dv_ours - dv_ref.view(b, C, P)).norm() / dv_ref.norm())
+        res[f"b{b}"] = {"reference_ms_fwd_bwd": ms_ref, "reference_cells_per_s": cells / (ms_ref * 1e-3),
+                        "reference_peak_extra_bytes": int(peak),
+                        "ours_ms_fwd_bwd": ms_ours, "ours_cells_per_s": cells / (ms_ours * 1e-3),
+                        "speedup": ms_ref / ms_ours, "launch": "eager (both)",
+                        "loss_reference": float(l_ref), "loss_ours": float(l_ours[0]),
+                        "dv_rel_err_vs_reference_fp32": err}
+        del v, a, dv_ref, dv_ours
+        torch.cuda.empty_cache()
+    return res
+
+
+def config1_reference_cpu(avt, cfg, dev):
+    """BASELINE.json configs[0] / SURVEY 8d config 1: the reference ITSELF -- AVENet(args, False) with its
+    ResNet-18 backbones (oracle/_ref), random init, image randn(8,3,224,224), audio randn(8,1,257,300),
+    fp32 on all host cores: (a) forward + CE, (b) + backward, (c) the similarity stage alone on the
+    pre-computed features; beside it this repo's AVENet on the GPU with the same inputs."""
+    import types
+    import numpy as np
+    import torch
+    from oracle import make_ref
+    ref_model, _ = make_ref.load()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    args = types.SimpleNamespace(epsilon=0.65, epsilon2=0.4, tri_map=True, Neg=True)
+    had_cuda = torch.cuda.is_available()
+    orig_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self            # keep model.py:115's mask on the CPU for this leg
+    try:
+        net = ref_model.AVENet(args, False)
+        image = torch.randn(8, 3, 224, 224)
+        audio = torch.randn(8, 1, 257, 300)
+        crit = torch.nn.CrossEntropyLoss()
+        tgt = torch.zeros(8).long()
+
+        def med(fn, n=3, warm=1):
+            for _ in range(warm):
+                fn()
+            ts = []
+            for _ in range(n):
+                t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
+            return float(np.median(ts))
+
+        def fwd():
+            with torch.no_grad():
+                return float(crit(net(image, audio)[1], tgt))
+
+        def fwd_bwd():
+            net.zero_grad(set_to_none=True)
+            loss = crit(net(image, audio)[1], tgt)
+            loss.backward()
+        t_a = med(fwd)
+        t_b = med(fwd_bwd, 2, 1)
+        with torch.no_grad():
+            img = net.imgnet(image)
+            aud = net.audnet(audio)
+        head = make_ref.reference_head()
+        aud_p = torch.nn.functional.adaptive_max_pool2d(aud, 1)
+
+        def stage():
+            vt = img.clone().requires_grad_(True); at = aud_p.clone().requires_grad_(True)
+            crit(head(vt, at)[1], tgt).backward()
+        t_c = med(stage, 10, 2)
+        loss_ref = fwd()
+    finally:
+        torch.Tensor.cuda = orig_cuda
+    res = {"cores": cores, "kind": "reference (oracle/_ref: unmodified model.py + models/base_models.py)",
+           "cells": 8 * 8 * P,
+           "a_forward_plus_ce_s": t_a, "b_forward_backward_s": t_b, "c_similarity_stage_fwd_bwd_s": t_c,
+           "clips_per_s_forward": 8 / t_a, "clips_per_s_train": 8 / t_b, "stage_cells_per_s": 8 * 8 * P / t_c,
+           "loss": loss_ref}
+    # this repo on the GPU, same inputs and the reference's weights (state-dict compatible names)
+    try:
+        ours = avt.AVENet(args, False, precision=cfg.precision).to(dev)
+        missing = ours.load_state_dict(net.state_dict(), strict=False)
+        ours.eval(); net.eval()
+        im_d, au_d = image.to(dev), audio.to(dev)
+
+        def g_fwd():
+            with torch.no_grad():
+                return ours.loss(im_d, au_d)
+        for _ in range(3):
+            l = g_fwd()
+        torch.cuda.synchronize()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for _ in range(10):
+            l = g_fwd()
+        s1.record(); torch.cuda.synchronize()
+        with torch.no_grad():
+            l_ref_eval = float(crit(net(image, audio)[1], tgt)) if not had_cuda else None
+        res["ours_gpu"] = {"forward_plus_ce_ms": s0.elapsed_time(s1) / 10, "loss_eval_mode": float(l),
+                           "state_dict_missing": list(missing.missing_keys)[:4],
+                           "state_dict_unexpected": list(missing.unexpected_keys)[:4]}
+    except Exception as e:                                   # noqa: BLE001
+        res["ours_gpu"] = {"error": repr(e)[:300]}
+    return res
+
+
+def extras_collective(avt, ev, _lib, cfg, dev, world, rank, barrier):
+    """Legs every rank takes part in: (1) train clips/s of the whole step -- stock-PyTorch ResNet-18
+    backbones under DDP (NCCL all-reduce of their gradients) + the row-sharded head with GLOBAL
+    negatives + Adam, 128 clips per rank (config 2, weak scaling; train_hardway_1frame.py:125-134);
+    (2) evaluation sharded over the ranks (maps are independent; integer success-curve counts
+    all-reduced, train_hardway_1frame.py:208-215)."""
+    import types
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    out = {}
+
+    def timed(fn, n, warm):
+        for _ in range(warm):
+            fn()
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for _ in range(n):
+            fn()
+        s1.record()
+        barrier()
+        t = torch.tensor([s0.elapsed_time(s1) / n], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    # ---- (1) train clips/s
+    args = types.SimpleNamespace(epsilon=0.65, epsilon2=0.4, tri_map=True, Neg=True)
+    torch.manual_seed(0)
+    net = avt.AVENet(args, False, precision=cfg.precision).to(dev).train()
+    model = net
+    if world > 1:
+        from torch.nn.parallel import DistributedDataParallel as DDP
+
+        class _Features(torch.nn.Module):                     # DDP wraps the part that has parameters
+            def __init__(self, n):
+                super().__init__(); self.n = n
+
+            def forward(self, image, audio):
+                return self.n.features(image, audio)
+        model = DDP(_Features(net), device_ids=[dev.index])
+    opt = torch.optim.Adam(net.parameters(), lr=1e-6, weight_decay=1e-4)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    img = torch.randn(128, 3, 224, 224, device=dev, generator=g)
+    spec = torch.randn(128, 1, 257, 300, device=dev, generator=g)
+    for tag, amp in (("fp32_backbones", False), ("bf16_autocast_backbones", True)):
         def train_step():
             opt.zero_grad(set_to_none=True)
-            loss = net.loss(img, spec)
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+                if world > 1:
+                    f_img, f_aud = model(img, spec)
+                else:
+                    f_img, f_aud = net.features(img, spec)
+            if world > 1:
+                loss = avt.dist.sharded_hardway_loss(f_img, f_aud.float(), net.head_config)
+            else:
+                loss = avt.hardway_loss(f_img, f_aud.float(), net.head_config)
             loss.backward()
             opt.step()
-        ms = timed(train_step, 5, 2)
-        out["train_cfg2_b128"] = {"clips_per_s": 128 / (ms * 1e-3), "ms_per_step": ms,
-                                  "note": "ResNet-18 backbones on stock PyTorch fp32 (as the reference runs them) dominate; head is libavtubes"}
-        try:                                                # same step, backbones under bf16 autocast
-            net = net.to(memory_format=torch.channels_last)
-            img_cl = img.contiguous(memory_format=torch.channels_last)
-            spec_cl = spec.contiguous(memory_format=torch.channels_last)
+        try:
+            ms = timed(train_step, 5, 2)
+            out[f"train_cfg2_b128_per_gpu_{tag}"] = {
+                "clips_per_s": world * 128 / (ms * 1e-3), "ms_per_step": ms, "n_gpus": world,
+                "global_batch": world * 128,
+                "note": "stock PyTorch ResNet-18 backbones" + (" under bf16 autocast (features reach the head as bf16)" if amp else " in fp32 (as the reference runs them)")
+                        + (", DDP gradient all-reduce; head row-sharded with global negatives" if world > 1 else "; head = libavtubes")
+                        + "; Adam(lr 1e-6, wd 1e-4)"}
+        except Exception as e:                               # noqa: BLE001
+            out[f"train_cfg2_b128_per_gpu_{tag}"] = {"error": repr(e)[:300]}
+    del net, model, opt, img, spec
+    torch.cuda.empty_cache()
 
-            def train_step_amp():
-                opt.zero_grad(set_to_none=True)
-                with torch.autocast("cuda", dtype=torch.bfloat16):
-                    loss = net.loss(img_cl, spec_cl)
-                loss.backward()
-                opt.step()
-            ms = timed(train_step_amp, 5, 2)
-            out["train_cfg2_b128_amp"] = {"clips_per_s": 128 / (ms * 1e-3), "ms_per_step": ms,
-                                          "note": "stock PyTorch backbones under bf16 autocast + channels_last; head unchanged (fp32 features in)"}
-        except Exception as e:
-            out["train_cfg2_b128_amp"] = {"error": repr(e)[:200]}
-    except Exception as e:                                  # keep the headline line alive
-        out["train_cfg2_b128"] = {"error": repr(e)[:200]}
+    # ---- (2) sharded evaluation: config 3's 5158 maps, real boxes, split over the ranks
+    from oracle import eval_oracle as eo
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "vggss_golden.npz"))
+    n = 5158
+    idx = np.arange(rank, n, world)
+    maps = torch.tensor(eo.synthetic_maps(n, 0)[idx], device=dev)
+    boxes = [gold["boxes"][i, :gold["count"][i]].tolist() for i in idx]
+    bx, bc = ev.pack_boxes(boxes, "vggss", max_boxes=7)
+    bx, bc = bx.to(dev), bc.to(dev)
+    state = {}
+
+    def eval_step():
+        r = ev.eval_maps_raw(maps, boxes=bx, box_count=bc, gt_mode="vggss")
+        if world > 1:
+            state["res"] = avt.dist.sharded_eval_counts(r["ciou"])
+        else:
+            state["res"] = ev.success_auc(r["ciou"])
+    ms = timed(eval_step, 5, 2)
+    e = {"maps_per_s": n / (ms * 1e-3), "ms": ms, "n_gpus": world,
+         "mode": "boxes in, scalars out; integer counts all-reduced" if world > 1 else "boxes in, scalars out"}
+    if world > 1:
+        half, auc, n_tot = state["res"]
+        e.update(auc=auc, ciou_at_half=half, n_total=n_tot, reference_auc=float(gold["auc"]))
+        assert n_tot == n and abs(auc - float(gold["auc"])) < 1e-3
+    out["eval_cfg3_sharded"] = e
     return out
 
 
@@ -608,6 +1037,9 @@ def emit(line: dict):
 
 _REAL_STDOUT = 1
 if __name__ == "__main__":
+    if len(sys.argv) == 3 and sys.argv[1] == "--eval-worker":
+        eval_worker(sys.argv[2])
+        sys.exit(0)
     sys.stdout.flush()
     _REAL_STDOUT = os.dup(1)
     os.dup2(2, 1)                      # fd 1 -> stderr for C libraries and stray prints
