@@ -175,13 +175,15 @@ def cpu_head_baseline(b_sample, steps, warmup, seed=1234):
 
         def one():
             return ho.reference_style_forward_torch(v.flatten(2), a.view(b_sample, C), backward=True)
-    for _ in range(warmup):
-        one()
-    ts = []
-    for _ in range(steps):
-        t0 = time.perf_counter()
-        one()
-        ts.append(time.perf_counter() - t0)
+    from oracle import make_ref as _mr
+    with _mr.cpu_shim():                                     # host tensors even where a GPU is visible
+        for _ in range(warmup):
+            one()
+        ts = []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            one()
+            ts.append(time.perf_counter() - t0)
     t = float(np.median(ts))
     cells = b_sample * b_sample * P
     what = ("the UNMODIFIED reference AVENet.forward (oracle/_ref, Identity backbones) + CrossEntropyLoss + backward"
@@ -383,8 +385,11 @@ def main():
 
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_base, _ = cpu_head_baseline(min(256, b_global), 3, 1)
-        cpu_base = {k: cpu_base[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        try:
+            cpu_base, _ = cpu_head_baseline(min(256, b_global), 3, 1)
+            cpu_base = {k: cpu_base[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as e:                               # noqa: BLE001  never lose the headline line
+            cpu_base = {"error": repr(e)[:300]}
 
     if rank == 0:
         line = {
@@ -854,9 +859,7 @@ def config1_reference_cpu(avt, cfg, dev):
     torch.set_num_threads(cores)
     torch.manual_seed(0)
     args = types.SimpleNamespace(epsilon=0.65, epsilon2=0.4, tri_map=True, Neg=True)
-    had_cuda = torch.cuda.is_available()
-    orig_cuda = torch.Tensor.cuda
-    torch.Tensor.cuda = lambda self, *a, **k: self            # keep model.py:115's mask on the CPU for this leg
+    shim = make_ref.cpu_shim().__enter__()                   # keep model.py:115's mask on the CPU for this leg
     try:
         net = ref_model.AVENet(args, False)
         image = torch.randn(8, 3, 224, 224)
@@ -894,7 +897,7 @@ def config1_reference_cpu(avt, cfg, dev):
         t_c = med(stage, 10, 2)
         loss_ref = fwd()
     finally:
-        torch.Tensor.cuda = orig_cuda
+        shim.__exit__()
     res = {"cores": cores, "kind": "reference (oracle/_ref: unmodified model.py + models/base_models.py)",
            "cells": 8 * 8 * P,
            "a_forward_plus_ce_s": t_a, "b_forward_backward_s": t_b, "c_similarity_stage_fwd_bwd_s": t_c,
@@ -918,8 +921,8 @@ def config1_reference_cpu(avt, cfg, dev):
         for _ in range(10):
             l = g_fwd()
         s1.record(); torch.cuda.synchronize()
-        with torch.no_grad():
-            l_ref_eval = float(crit(net(image, audio)[1], tgt)) if not had_cuda else None
+        with make_ref.cpu_shim(), torch.no_grad():           # the reference in eval mode, same weights
+            res["loss_eval_mode"] = float(crit(net(image, audio)[1], tgt))
         res["ours_gpu"] = {"forward_plus_ce_ms": s0.elapsed_time(s1) / 10, "loss_eval_mode": float(l),
                            "state_dict_missing": list(missing.missing_keys)[:4],
                            "state_dict_unexpected": list(missing.unexpected_keys)[:4]}

@@ -68,6 +68,23 @@ def available() -> bool:
 _loaded = None
 
 
+class cpu_shim:
+    """``with cpu_shim():`` -- run the reference on HOST tensors where a GPU is present: model.py:115
+    (and :48-51) call ``.cuda()`` on the mask they build, which would put it on the GPU while the
+    features are on the CPU.  Inside the block ``Tensor.cuda`` is the identity (SURVEY.md 8c's shim)."""
+
+    def __enter__(self):
+        import torch
+        self._orig = torch.Tensor.cuda
+        torch.Tensor.cuda = lambda t, *a, **k: t
+        return self
+
+    def __exit__(self, *exc):
+        import torch
+        torch.Tensor.cuda = self._orig
+        return False
+
+
 def load():
     """(ref_model, ref_utils): the staged reference modules, imported unmodified."""
     global _loaded
