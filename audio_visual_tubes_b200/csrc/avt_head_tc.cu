@@ -18,11 +18,14 @@
 //              step by the blocks of all audio tiles, so each image is read from HBM once
 #include "avt_common.cuh"
 #include "avt_tc.cuh"
+#include <stdlib.h>
 
 namespace avt {
 using namespace tc;
 
-constexpr int kTcThreads = 320;                         // warp 0 TMA, 1 MMA, 2..9 epilogue
+constexpr int kColGroups = 4;                           // epilogue warps per TMEM lane quarter
+constexpr int kEpiWarps = 4 * kColGroups;
+constexpr int kTcThreads = 64 + 32 * kEpiWarps;         // warp 0 TMA, 1 MMA, 2..17 epilogue
 constexpr int kBM = 128;
 constexpr int kBN = 208;
 constexpr int kBK = 64;
@@ -32,68 +35,117 @@ constexpr int kABytes = kBM * kBK * 2;                  // 16384 per K chunk
 constexpr int kBBytes = kBN * kBK * 2;                  // 26624 per stage
 constexpr int kAccCols = 256;
 constexpr int kTmemCols = 512;
-constexpr size_t kTcSmemBytes = 1024 + (size_t)kMaxKC * kABytes + (size_t)kStagesB * kBBytes + 256 + 2 * kBM * 8;
+constexpr int kStagesBPair = 7;                         // cta_group::2: half a B tile (13 KB) per CTA and stage
+constexpr int kPartBytes = 2 * (kColGroups - 1) * kBM * 8;
+constexpr size_t kTcSmemBytes = 1024 + (size_t)kMaxKC * kABytes + (size_t)kStagesB * kBBytes + 256 + kPartBytes;
+constexpr size_t kTcSmemBytesPair = 1024 + (size_t)kMaxKC * kABytes + (size_t)kStagesBPair * (kBBytes / 2) + 256 + kPartBytes;
+static_assert(kTcSmemBytesPair <= 232448 && kTcSmemBytes <= 232448, "shared memory budget (227 KB)");
+static_assert((kBBytes / 2) % 1024 == 0, "half a B tile must keep the 1024-byte swizzle alignment");
+
+// ---- packed fp32 pairs (sm_100: FFMA2 / FMUL2 / FADD2 issue one instruction for two lanes' worth
+// of fp32 work).  The epilogues below are instruction-issue bound (ncu, round 2: 18 instructions per
+// cell in the gradient epilogue, issue slots 50 % busy at 2 warps per scheduler), so every
+// elementwise step is written on float2.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    float2 d;
+    asm("{.reg .b64 ra, rb, rc, rd;\n\t"
+        "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+        "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
+        "mov.b64 {%0, %1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+    float2 d;
+    asm("{.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+        "mul.rn.f32x2 rd, ra, rb;\n\tmov.b64 {%0, %1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return d;
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+    float2 d;
+    asm("{.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+        "add.rn.f32x2 rd, ra, rb;\n\tmov.b64 {%0, %1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return d;
+}
+__device__ __forceinline__ float2 splat(float x) { return make_float2(x, x); }
 
 // One chunk of N accumulator columns of one TMEM lane.  w = sigma((s - eps)/tau) =
-// 1 / (1 + 2^(s*c1 + c0)).  The fast variant shares one MUFU.RCP between two cells
-// (r = 1/(x0*x1); w0 = r*x1; w1 = r*x0), which needs the exponent clamped so the product
-// cannot overflow; clamped cells only matter when EVERY weight of the (n, k) pair is below
-// 2^-30, and in that case the caller redoes the pair with kExact = true (one RCP per cell,
-// no clamp), so results never depend on the clamp.
+// 1 / (1 + 2^(s*c1 + c0)).  Fast variant: two cells share one MUFU.RCP (r = 1/(x0*x1); w0 = r*x1;
+// w1 = r*x0) -- 1.5 MUFU operations per cell instead of 2 (the forward epilogue at 2 per cell was
+// MUFU-bound: 3136 of the 3328 clocks an image tile's MMAs take).  The product x0*x1 overflows only
+// when both weights are below 2^-64; such cells then read 0, which matters only when EVERY weight
+// of the (n, k) pair is tiny -- the caller detects that (den below 2^-30) and redoes the pair with
+// kExact = true (one RCP per cell), so results never depend on it.
 struct CellCtx {
     float c1, c0, itau;          // sigmoid constants
     float sm, coef;              // backward: pooled sim and gsim / den of this (n, k)
 };
-constexpr float kExpClamp = 60.0f;
 constexpr float kTinyDen = 9.313225746154785e-10f;      // 2^-30
+constexpr float kTinyFwd = 8.8817841970012523e-16f;     // 2^-50 per column: forward redo threshold
 
-template <bool kGrad, bool kExact, int N>
-__device__ __forceinline__ void cell_chunk(const uint32_t (&r)[N], const CellCtx& cx, float& num,
-                                           float& dn, __half* gp, uint32_t pitch) {
+// kPitch: compile-time row pitch of G in elements (0 = run-time `pitch`), so that the 32 stores of
+// a chunk are STG [base + immediate] instead of one 64-bit address add each
+template <bool kGrad, bool kExact, int N, int kPitch>
+__device__ __forceinline__ void cell_chunk(const uint32_t (&r)[N], const CellCtx& cx, float2& num,
+                                           float2& dn, __half* gp, uint32_t pitch_rt) {
+    const uint32_t pitch = kPitch ? (uint32_t)kPitch : pitch_rt;
 #pragma unroll
     for (int i = 0; i < N; i += 2) {
-        const float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
-        float w0, w1;
+        const float2 s = make_float2(__uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+        const float2 t = ffma2(s, splat(cx.c1), splat(cx.c0));
+        const float2 x = fadd2(make_float2(fast_ex2(t.x), fast_ex2(t.y)), splat(1.0f));
+        float2 w;
         if (kExact) {
-            w0 = fast_rcp(1.0f + fast_ex2(fmaf(s0, cx.c1, cx.c0)));
-            w1 = fast_rcp(1.0f + fast_ex2(fmaf(s1, cx.c1, cx.c0)));
+            w = make_float2(fast_rcp(x.x), fast_rcp(x.y));
         } else {
-            const float x0 = 1.0f + fast_ex2(fminf(fmaf(s0, cx.c1, cx.c0), kExpClamp));
-            const float x1 = 1.0f + fast_ex2(fminf(fmaf(s1, cx.c1, cx.c0), kExpClamp));
-            const float rr = fast_rcp(x0 * x1);
-            w0 = rr * x1;
-            w1 = rr * x0;
+            const float rr = fast_rcp(x.x * x.y);
+            w = make_float2(rr * x.y, rr * x.x);
         }
         if (kGrad) {
-            const float g0 = (cx.coef * w0) * fmaf(s0 - cx.sm, fmaf(-w0, cx.itau, cx.itau), 1.0f);
-            const float g1 = (cx.coef * w1) * fmaf(s1 - cx.sm, fmaf(-w1, cx.itau, cx.itau), 1.0f);
-            gp[(uint32_t)i * pitch] = __float2half_rn(g0);
-            gp[(uint32_t)(i + 1) * pitch] = __float2half_rn(g1);
+            // G = coef w (1 + (s - sim)(1 - w)/tau)
+            const float2 u = ffma2(w, splat(-cx.itau), splat(cx.itau));
+            const float2 f = ffma2(fadd2(s, splat(-cx.sm)), u, splat(1.0f));
+            const float2 gv = fmul2(fmul2(w, splat(cx.coef)), f);
+            const __half2 h = __floats2half2_rn(gv.x, gv.y);
+            gp[(uint32_t)i * pitch] = __low2half(h);
+            gp[(uint32_t)(i + 1) * pitch] = __high2half(h);
         } else {
-            dn += w0 + w1;
-            num = fmaf(w0, s0, num);
-            num = fmaf(w1, s1, num);
+            dn = fadd2(dn, w);
+            num = ffma2(w, s, num);
         }
     }
 }
 
 // all columns [c_begin, c_end) of one TMEM lane (c_end - c_begin a multiple of 4)
-template <bool kGrad, bool kExact>
+template <bool kGrad, bool kExact, int kPitch>
 __device__ __forceinline__ void cell_sweep(uint32_t taddr, int c_begin, int c_end, const CellCtx& cx,
-                                           float& num, float& dn, __half* gout, uint32_t pitch) {
+                                           float& num_out, float& dn_out, __half* gout, uint32_t pitch_rt) {
+    const uint32_t pitch = kPitch ? (uint32_t)kPitch : pitch_rt;
+    float2 num = make_float2(0.f, 0.f), dn = make_float2(0.f, 0.f);
     int c = c_begin;
     for (; c + 32 <= c_end; c += 32) {
         uint32_t r[32];
         tmem_ld_32x32(taddr + c, r);
         tmem_ld_wait();
-        cell_chunk<kGrad, kExact, 32>(r, cx, num, dn, gout + (uint32_t)c * pitch, pitch);
+        cell_chunk<kGrad, kExact, 32, kPitch>(r, cx, num, dn, gout + (uint32_t)c * pitch, pitch_rt);
+    }
+    if (c + 16 <= c_end) {
+        uint32_t r[16];
+        tmem_ld_32x16(taddr + c, r);
+        tmem_ld_wait();
+        cell_chunk<kGrad, kExact, 16, kPitch>(r, cx, num, dn, gout + (uint32_t)c * pitch, pitch_rt);
+        c += 16;
     }
     for (; c < c_end; c += 4) {
         uint32_t r[4];
         tmem_ld_32x4(taddr + c, r);
         tmem_ld_wait();
-        cell_chunk<kGrad, kExact, 4>(r, cx, num, dn, gout + (uint32_t)c * pitch, pitch);
+        cell_chunk<kGrad, kExact, 4, kPitch>(r, cx, num, dn, gout + (uint32_t)c * pitch, pitch_rt);
     }
+    num_out = num.x + num.y;
+    dn_out = dn.x + dn.y;
 }
 
 // kGrad = false: forward (writes sim / den / logits).
@@ -101,70 +153,95 @@ __device__ __forceinline__ void cell_sweep(uint32_t taddr, int c_begin, int c_en
 //   every cell into its gradient  G = gsim/den * w (1 + (S - sim)(1 - w)/tau)  (+ GA on the
 //   positive column), stored as fp16 in G[n*P + p][k] (row pitch n_a_pad) --
 //   the K-major A operand of the dv contraction and the MN-major A operand of the d_ahat one.
-template <bool kGrad>
+// kPair = true : tcgen05.mma.cta_group::2.  A cluster of two CTAs owns TWO audio tiles (M = 256) of
+//   the same image: each CTA keeps its own 128 audio rows resident and receives its own 128
+//   accumulator lanes, but streams only HALF of the image tile (104 of the 208 rows of B) -- the
+//   hardware reads both halves across the pair.  ncu of the 1-CTA kernel (profiles/r2_ncu_head_a):
+//   tensor pipe 61 % with the L2 and the crossbar at ~30 %: with A resident only 3 x 26 KB of B
+//   fit in flight per SM against 64 B/clk needed -- latency-bound on the operand feed.  In pair
+//   mode a CTA needs 32 B/clk and holds 7 stages of 13 KB.
+template <bool kGrad, bool kPair, int kPitch>
 __global__ void __launch_bounds__(kTcThreads, 1)
 sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                const int32_t* __restrict__ pos_idx, int col_offset, int N_v, int N_a, int n_mt,
-                int groups, int KC, int P, HeadParams hp, int L, float* __restrict__ logits,
-                float* __restrict__ sim, float* __restrict__ den,
-                const float* __restrict__ gsim, const float* __restrict__ GA,
-                __half* __restrict__ G, int n_a_pad, const unsigned int* __restrict__ gmax_bits) {
+              const int32_t* __restrict__ pos_idx, int col_offset, int N_v, int N_a, int n_mt,
+              int groups, int KC, int P, HeadParams hp, int L, float* __restrict__ logits,
+              float* __restrict__ sim, float* __restrict__ den,
+              const float* __restrict__ gsim, const float* __restrict__ GA,
+              __half* __restrict__ G, int n_a_pad, const unsigned int* __restrict__ gmax_bits) {
+    constexpr int kStages = kPair ? kStagesBPair : kStagesB;
+    constexpr int kStageBytes = kPair ? kBBytes / 2 : kBBytes;
+    constexpr uint32_t kEpiArrivals = (uint32_t)(kEpiWarps * 32) * (kPair ? 2u : 1u);
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sA = base;
     uint8_t* sB = sA + (size_t)kMaxKC * kABytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)kStagesB * kBBytes);
-    uint64_t* full_b = bars;                             // [kStagesB]
-    uint64_t* empty_b = bars + kStagesB;                 // [kStagesB]
-    uint64_t* a_full = bars + 2 * kStagesB;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)kStages * kStageBytes);
+    uint64_t* full_b = bars;                             // [kStages]  (pair: the leader's copy counts both CTAs' bytes)
+    uint64_t* empty_b = bars + kStages;                  // [kStages]
+    uint64_t* a_full = bars + 2 * kStages;
     uint64_t* a_empty = a_full + 1;
     uint64_t* tmem_full = a_empty + 1;                   // [2]
-    uint64_t* tmem_empty = tmem_full + 2;                // [2]
+    uint64_t* tmem_empty = tmem_full + 2;                // [2]  (pair: leader's copies, arrivals of both CTAs)
     uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-    float2* part = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][kBM]
+    float2* part = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][kColGroups-1][kBM]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int mt0 = blockIdx.x / groups, g = blockIdx.x % groups, mt_step = gridDim.x / groups;
+    const uint32_t rank = kPair ? cluster_ctarank() : 0u;
+    // work item of a block (pair): audio tile (pair) u0, u0 + u_step, ...; images g, g + groups, ...
+    const int unit = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int n_units = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int n_ut = kPair ? n_mt / 2 : n_mt;            // audio tiles (pairs) in total
+    const int u0 = unit / groups, g = unit % groups, u_step = n_units / groups;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&map_a);
         prefetch_tmap(&map_b);
-        for (int i = 0; i < kStagesB; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
+        for (int i = 0; i < kStages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
         mbar_init(a_full, 1);
         mbar_init(a_empty, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 256); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], kEpiArrivals); }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_holder, kTmemCols);
+    if (warp == 1) { if (kPair) tmem_alloc2(tmem_holder, kTmemCols); else tmem_alloc(tmem_holder, kTmemCols); }
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync();                           // both CTAs' barriers exist before any remote arrive
     tc_fence_after();
     const uint32_t tmem_base = *tmem_holder;
 
     if (warp == 0) {
-        if (lane == 0) {                                 // ---------------- TMA producer
+        if (lane == 0) {                                 // ---------------- TMA producer (both CTAs of a pair)
             int stage = 0; uint32_t phase = 0, a_par = 0;
-            for (int mt = mt0; mt < n_mt; mt += mt_step) {
-                if (mt != mt0) { mbar_wait(a_empty, a_par); a_par ^= 1; }
-                mbar_arrive_expect_tx(a_full, (uint32_t)(KC * kABytes));
-                for (int kc = 0; kc < KC; ++kc)
-                    tma_load_2d(sA + (size_t)kc * kABytes, &map_a, a_full, kc * kBK, mt * kBM);
+            for (int u = u0; u < n_ut; u += u_step) {
+                const int mt = kPair ? 2 * u + (int)rank : u;
+                if (u != u0) { mbar_wait(a_empty, a_par); a_par ^= 1; }
+                if (!kPair || rank == 0) mbar_arrive_expect_tx(a_full, (uint32_t)(KC * kABytes) * (kPair ? 2u : 1u));
+                for (int kc = 0; kc < KC; ++kc) {
+                    if (kPair) tma_load_2d_pair(sA + (size_t)kc * kABytes, &map_a, a_full, kc * kBK, mt * kBM);
+                    else tma_load_2d(sA + (size_t)kc * kABytes, &map_a, a_full, kc * kBK, mt * kBM);
+                }
                 for (int n = g; n < N_v; n += groups) {
                     for (int kc = 0; kc < KC; ++kc) {
                         mbar_wait(&empty_b[stage], phase ^ 1);
-                        mbar_arrive_expect_tx(&full_b[stage], (uint32_t)kBBytes);
-                        tma_load_2d(sB + (size_t)stage * kBBytes, &map_b, &full_b[stage], kc * kBK, n * P);
-                        if (++stage == kStagesB) { stage = 0; phase ^= 1; }
+                        if (kPair) {
+                            if (rank == 0) mbar_arrive_expect_tx(&full_b[stage], (uint32_t)kBBytes);
+                            tma_load_2d_pair(sB + (size_t)stage * kStageBytes, &map_b, &full_b[stage], kc * kBK,
+                                             n * P + (int)rank * (kBN / 2));
+                        } else {
+                            mbar_arrive_expect_tx(&full_b[stage], (uint32_t)kBBytes);
+                            tma_load_2d(sB + (size_t)stage * kStageBytes, &map_b, &full_b[stage], kc * kBK, n * P);
+                        }
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {                                 // ---------------- MMA issuer
-            const uint32_t idesc = make_idesc_f16(kBM, kBN, 0, 0);
+        if (lane == 0 && rank == 0) {                    // ---------------- MMA issuer (pair: the leader only)
+            const uint32_t idesc = make_idesc_f16(kPair ? 2 * kBM : kBM, kBN, 0, 0);
             int stage = 0; uint32_t phase = 0, a_par = 0;
             uint32_t tile = 0;
-            for (int mt = mt0; mt < n_mt; mt += mt_step) {
+            for (int u = u0; u < n_ut; u += u_step) {
                 mbar_wait(a_full, a_par); a_par ^= 1;
                 tc_fence_after();
                 for (int n = g; n < N_v; n += groups, ++tile) {
@@ -176,28 +253,31 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                         mbar_wait(&full_b[stage], phase);
                         tc_fence_after();
                         const uint32_t a_addr = smem_u32(sA + (size_t)kc * kABytes);
-                        const uint32_t b_addr = smem_u32(sB + (size_t)stage * kBBytes);
+                        const uint32_t b_addr = smem_u32(sB + (size_t)stage * kStageBytes);
 #pragma unroll
                         for (int k = 0; k < kBK / 16; ++k) {
                             const uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
                             const uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
-                            umma_f16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                            if (kPair) umma2_f16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                            else umma_f16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
                         }
-                        umma_commit(&empty_b[stage]);    // frees the stage once these MMAs retire
-                        if (++stage == kStagesB) { stage = 0; phase ^= 1; }
+                        // frees the stage (in both CTAs) once these MMAs retire
+                        if (kPair) umma2_commit_mc(&empty_b[stage], 3); else umma_commit(&empty_b[stage]);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
-                    umma_commit(&tmem_full[buf]);
+                    if (kPair) umma2_commit_mc(&tmem_full[buf], 3); else umma_commit(&tmem_full[buf]);
                 }
-                umma_commit(a_empty);
+                if (kPair) umma2_commit_mc(a_empty, 3); else umma_commit(a_empty);
             }
         }
-    } else {                                             // ---------------- epilogue warps 2..9
-        // two warps per TMEM lane quarter (one per scheduler pair): each takes half of the
-        // image's positions, so every SM sub-partition has two warps to hide MUFU / TMEM latency
+    } else {                                             // ---------------- epilogue warps 2 .. 2 + kEpiWarps
+        // kColGroups warps per TMEM lane quarter (one per scheduler each): every warp takes a slice of
+        // the image's positions, so each SM sub-partition has four warps to hide MUFU / TMEM latency
+        // (ncu of the 2-group version: issue slots 50 % busy, tensor pipe 46 % -- latency-bound)
         const int q = warp & 3;                          // TMEM lane quarter this warp may touch
-        const int half = (warp - 2) >> 2;
-        const int split = ((P >> 1) >> 5) << 5;          // 96 for P = 196
-        const int c_begin = half ? split : 0, c_end = half ? P : split;
+        const int grp = (warp - 2) >> 2;                 // column group 0 .. kColGroups-1
+        const int cw = ((P / kColGroups) >> 4) << 4;     // 48 for P = 196; the last group takes the rest
+        const int c_begin = grp * cw, c_end = (grp == kColGroups - 1) ? P : (grp + 1) * cw;
         const int row = q * 32 + lane;
         const float c1 = -kLog2e / hp.tau, c0 = hp.eps * kLog2e / hp.tau;
         const float itemp = 1.0f / hp.temp, itau = 1.0f / hp.tau;
@@ -206,7 +286,8 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
         // by the two contractions that consume them
         const float gscale = kGrad ? pow2i(g_scale_exp(__ldg(gmax_bits))) : 1.0f;
         uint32_t tile = 0;
-        for (int mt = mt0; mt < n_mt; mt += mt_step) {
+        for (int u = u0; u < n_ut; u += u_step) {
+            const int mt = kPair ? 2 * u + (int)rank : u;
             const int k = mt * kBM + row;
             // per-(n, k) coefficients of the NEXT tile are requested while this one is swept, so
             // their global-load latency never sits between the accumulator and the sweep
@@ -240,12 +321,16 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccCols;
                 float num = 0.f, dn = 0.f;
-                // forward: MMA-bound, one RCP per cell is free; backward: MUFU-bound, share RCPs
-                // unless some pair of this warp has every weight below 2^-30 (rare)
-                if (!kGrad || exact) cell_sweep<kGrad, true>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
-                else cell_sweep<kGrad, false>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
+                // two cells share one RCP unless some pair of this warp has every weight tiny (rare): the
+                // backward knows from the saved den, the forward from the sum it has just formed (the
+                // accumulator is still there, so the slice is simply swept again)
+                if (kGrad && exact) cell_sweep<kGrad, true, kPitch>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
+                else cell_sweep<kGrad, false, kPitch>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
+                if (!kGrad && __any_sync(0xffffffffu, !(dn >= kTinyFwd * (float)(c_end - c_begin))))
+                    cell_sweep<false, true, 0>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
                 tc_fence_before();
-                mbar_arrive(&tmem_empty[buf]);           // accumulator may be overwritten
+                // accumulator may be overwritten (pair: the leader's barrier collects both CTAs)
+                if (!kPair || rank == 0) mbar_arrive(&tmem_empty[buf]); else mbar_arrive_leader(&tmem_empty[buf]);
                 if (kGrad) {
                     // positive column: G[n, pos, p] += GA[n, p] (gradient through A, sim1, sim2).
                     // The whole warp shares the fix-up of its one positive lane.
@@ -260,13 +345,16 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                         }
                     }
                 }
-                if (!kGrad) {                            // combine the two column halves
-                    float2* pp = part + (tile & 1u) * kBM;
-                    if (half) pp[row] = make_float2(num, dn);
-                    asm volatile("bar.sync 1, 256;" ::: "memory");
-                    if (!half) { const float2 o = pp[row]; num += o.x; dn += o.y; }
+                if (!kGrad) {                            // combine the column groups
+                    float2* pp = part + (tile & 1u) * (kColGroups - 1) * kBM;
+                    if (grp) pp[(grp - 1) * kBM + row] = make_float2(num, dn);
+                    asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+                    if (!grp) {
+#pragma unroll
+                        for (int j = 0; j < kColGroups - 1; ++j) { const float2 o = pp[j * kBM + row]; num += o.x; dn += o.y; }
+                    }
                 }
-                if (!kGrad && !half && k < N_a) {
+                if (!kGrad && !grp && k < N_a) {
                     const float smv = num / dn;
                     const float m = (k == pos) ? (1.0f - hp.mask_scale) : 1.0f;
                     sim[(size_t)n * N_a + k] = smv;
@@ -278,51 +366,82 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
     }
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync();                           // nobody leaves while the pair may still touch its smem / TMEM
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, kTmemCols);
+        if (kPair) tmem_dealloc2(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols);
     }
+}
+
+template <bool kGrad, bool kPair, int kPitch>
+static int launch_sim_variant(const CUtensorMap& map_a, const CUtensorMap& map_b, int grid, size_t smem,
+                              const int32_t* pos_idx, int col_offset, int N_v, int N_a, int n_mt, int groups,
+                              int KC, int P, HeadParams hp, int L, float* logits, float* sim, float* den,
+                              const float* gsim, const float* GA, __half* G, int n_a_pad,
+                              const unsigned int* gmax_bits, cudaStream_t st) {
+    auto kernel = sim_tc_kernel<kGrad, kPair, kPitch>;
+    AVT_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kTcThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kPair ? 2 : 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AVT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, pos_idx, col_offset, N_v, N_a, n_mt, groups, KC,
+                                      P, hp, L, logits, sim, den, gsim, GA, G, n_a_pad, gmax_bits));
+    AVT_LAUNCH_CHECK();
+    return AVT_OK;
 }
 
 static int launch_sim_tc(bool grad, const __half* vt, const __half* a_h,
                          const int32_t* pos_idx, int col_offset, int N_v, int N_a, int C, int P,
                          HeadParams hp, float* logits, float* sim, float* den, const float* gsim,
-                         const float* GA, __half* G, int n_a_pad, const unsigned int* gmax_bits,
+                         const float* GA, __half* G, int n_a_pad_in, const unsigned int* gmax_bits,
                          cudaStream_t st) {
+    const int n_a_pad = n_a_pad_in ? n_a_pad_in : n_a_padded(N_a);      // rows of a_h (zero rows past N_a)
     AVT_REQUIRE(C % kBK == 0 && C <= kMaxKC * kBK, "fp16 head: C=%d must be a multiple of 64, <= 512", C);
     AVT_REQUIRE(P % 4 == 0 && P <= kBN, "fp16 head: P=%d must be a multiple of 4, <= 208", P);
     // backward: every column of G up to n_a_pad must be written (pad columns get zeros)
-    const int n_mt = grad ? n_a_pad / kBM : (N_a + kBM - 1) / kBM;
+    int n_mt = grad ? n_a_pad / kBM : (N_a + kBM - 1) / kBM;
+    static const bool no_pair = getenv("AVT_NO_PAIR") != nullptr;           // development switch, read once
+    const bool pair = !no_pair && n_a_pad >= 2 * kBM;                        // n_a_pad is then a multiple of 256
+    if (pair) n_mt = (n_mt + 1) / 2 * 2;                                     // whole tile pairs (a_h rows are padded)
     CUtensorMap map_a, map_b;
-    if (!make_tmap_f16_2d(&map_a, a_h, (uint64_t)n_mt * kBM, (uint64_t)C, (uint64_t)C * 2, kBK, kBM) ||
-        !make_tmap_f16_2d(&map_b, vt, (uint64_t)N_v * P, (uint64_t)C, (uint64_t)C * 2, kBK, kBN)) {
+    if (!make_tmap_f16_2d(&map_a, a_h, (uint64_t)n_a_pad, (uint64_t)C, (uint64_t)C * 2, kBK, kBM) ||
+        !make_tmap_f16_2d(&map_b, vt, (uint64_t)N_v * P, (uint64_t)C, (uint64_t)C * 2, kBK, pair ? kBN / 2 : kBN)) {
         set_error("fp16 head: cuTensorMapEncodeTiled failed");
         return AVT_ERR_CUDA;
     }
     int dev = 0, sms = 148;
     AVT_CHECK_CUDA(cudaGetDevice(&dev));
     AVT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int mt_par = n_mt < sms ? n_mt : sms;
-    int groups = sms / mt_par;
+    const int slots = pair ? sms / 2 : sms;              // CTAs (or CTA pairs) resident at once
+    const int n_ut = pair ? n_mt / 2 : n_mt;
+    const int ut_par = n_ut < slots ? n_ut : slots;
+    int groups = slots / ut_par;
     if (groups > N_v) groups = N_v;
     if (groups < 1) groups = 1;
-    const int grid = groups * mt_par;
+    const int grid = groups * ut_par * (pair ? 2 : 1);
     const int L = N_a + 1 + (hp.use_neg ? 1 : 0);
-    if (grad) {
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)kTcSmemBytes));
-        sim_tc_kernel<true><<<grid, kTcThreads, kTcSmemBytes, st>>>(
-            map_a, map_b, pos_idx, col_offset, N_v, N_a, n_mt, groups, C / kBK, P, hp, L, logits, sim, den,
-            gsim, GA, G, n_a_pad, gmax_bits);
-    } else {
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(sim_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)kTcSmemBytes));
-        sim_tc_kernel<false><<<grid, kTcThreads, kTcSmemBytes, st>>>(
-            map_a, map_b, pos_idx, col_offset, N_v, N_a, n_mt, groups, C / kBK, P, hp, L, logits, sim, den,
-            nullptr, nullptr, nullptr, 0, nullptr);
+    const int KC = C / kBK;
+#define AVT_SIM(GR, PR, PI)                                                                               \
+    launch_sim_variant<GR, PR, PI>(map_a, map_b, grid, PR ? kTcSmemBytesPair : kTcSmemBytes, pos_idx, col_offset, N_v, \
+                                   N_a, n_mt, groups, KC, P, hp, L, logits, sim, den, gsim, GA, G, n_a_pad, gmax_bits, st)
+    if (!grad) return pair ? AVT_SIM(false, true, 0) : AVT_SIM(false, false, 0);
+    if (!pair) return n_a_pad == 128 ? AVT_SIM(true, false, 128) : AVT_SIM(true, false, 0);
+    switch (n_a_pad) {                                   // common audio counts get immediate store offsets
+        case 256: return AVT_SIM(true, true, 256);
+        case 512: return AVT_SIM(true, true, 512);
+        case 1024: return AVT_SIM(true, true, 1024);
+        default: return AVT_SIM(true, true, 0);
     }
-    AVT_LAUNCH_CHECK();
-    return AVT_OK;
+#undef AVT_SIM
 }
 
 int launch_sim_f16(const __half* vt, const __half* a_h, const int32_t* pos_idx,
