@@ -13,7 +13,7 @@
 //                  rows 196..207 of a box belong to the next image (or are zero-filled past
 //                  the end) and land in accumulator columns nobody reads
 //   TMEM       2 accumulators x 256 columns: the epilogue of tile i overlaps the MMAs of i+1
-//   warps      0: TMA producer   1: MMA issuer + TMEM owner   2-5: epilogue (one lane quarter each)
+//   warps      0-15: epilogue (lane quarter = warp % 4, four column groups)   16: TMA producer   17: MMA issuer + TMEM owner
 //   grid       persistent: block = (audio tile, image group); images of a group are visited in
 //              step by the blocks of all audio tiles, so each image is read from HBM once
 #include "avt_common.cuh"
@@ -25,7 +25,13 @@ using namespace tc;
 
 constexpr int kColGroups = 4;                           // epilogue warps per TMEM lane quarter
 constexpr int kEpiWarps = 4 * kColGroups;
-constexpr int kTcThreads = 64 + 32 * kEpiWarps;         // warp 0 TMA, 1 MMA, 2..17 epilogue
+constexpr int kTcThreads = 64 + 32 * kEpiWarps;         // warps 0..15 epilogue, 16 TMA, 17 MMA
+// The two single-thread roles sit at the HIGHEST warp ids: the sub-partition arbiter prefers the
+// highest warp id among eligible warps, and the MMA issuer shares its scheduler with four epilogue
+// warps -- as warp 1 it only issued when all four were stalled (cycle trace, round 2: the issuer spent
+// 85 % of its time in its own ~70 instructions per K chunk, 144 clocks per MMA against the 104 the
+// tensor pipe needs).
+constexpr int kWarpTma = kEpiWarps, kWarpMma = kEpiWarps + 1;
 constexpr int kBM = 128;
 constexpr int kBN = 208;
 constexpr int kBK = 64;
@@ -160,6 +166,16 @@ __device__ __forceinline__ void cell_sweep(uint32_t taddr, int c_begin, int c_en
 //   tensor pipe 61 % with the L2 and the crossbar at ~30 %: with A resident only 3 x 26 KB of B
 //   fit in flight per SM against 64 B/clk needed -- latency-bound on the operand feed.  In pair
 //   mode a CTA needs 32 B/clk and holds 7 stages of 13 KB.
+#ifdef AVT_TC_TRACE
+// development build only (-DAVT_TC_TRACE): per-block cycle counters of the MMA issuer and of one
+// epilogue warp -- [0] issuer waiting for operands, [1] issuer waiting for a free accumulator,
+// [2] issuer total, [3] epilogue waiting for the accumulator, [4] epilogue sweeping, [5] epilogue total
+__device__ unsigned long long g_tc_trace[1024 * 8];
+#define AVT_TRACE(x) x
+#else
+#define AVT_TRACE(x)
+#endif
+
 template <bool kGrad, bool kPair, int kPitch>
 __global__ void __launch_bounds__(kTcThreads, 1)
 sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
@@ -193,7 +209,7 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
     const int n_ut = kPair ? n_mt / 2 : n_mt;            // audio tiles (pairs) in total
     const int u0 = unit / groups, g = unit % groups, u_step = n_units / groups;
 
-    if (warp == 0 && lane == 0) {
+    if (warp == kWarpTma && lane == 0) {
         prefetch_tmap(&map_a);
         prefetch_tmap(&map_b);
         for (int i = 0; i < kStages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
@@ -202,14 +218,14 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
         for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], kEpiArrivals); }
         fence_barrier_init();
     }
-    if (warp == 1) { if (kPair) tmem_alloc2(tmem_holder, kTmemCols); else tmem_alloc(tmem_holder, kTmemCols); }
+    if (warp == kWarpMma) { if (kPair) tmem_alloc2(tmem_holder, kTmemCols); else tmem_alloc(tmem_holder, kTmemCols); }
     tc_fence_before();
     __syncthreads();
     if (kPair) cluster_sync();                           // both CTAs' barriers exist before any remote arrive
     tc_fence_after();
     const uint32_t tmem_base = *tmem_holder;
 
-    if (warp == 0) {
+    if (warp == kWarpTma) {
         if (lane == 0) {                                 // ---------------- TMA producer (both CTAs of a pair)
             int stage = 0; uint32_t phase = 0, a_par = 0;
             for (int u = u0; u < n_ut; u += u_step) {
@@ -236,46 +252,61 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                 }
             }
         }
-    } else if (warp == 1) {
-        if (lane == 0 && rank == 0) {                    // ---------------- MMA issuer (pair: the leader only)
+    } else if (warp == kWarpMma) {
+        if (rank == 0) {                                 // ---------------- MMA issuer (pair: the leader only)
+            // the whole warp walks the loops (uniform control flow, uniform registers); one elected
+            // lane issues the MMAs and their commits
             const uint32_t idesc = make_idesc_f16(kPair ? 2 * kBM : kBM, kBN, 0, 0);
+            const uint64_t a_desc0 = make_smem_desc(smem_u32(sA), 16, 1024);
+            const uint64_t b_desc0 = make_smem_desc(smem_u32(sB), 16, 1024);
             int stage = 0; uint32_t phase = 0, a_par = 0;
             uint32_t tile = 0;
+            AVT_TRACE(long long tw_full = 0; long long tw_empty = 0; const long long t_begin = clock64(); long long t0;)
             for (int u = u0; u < n_ut; u += u_step) {
                 mbar_wait(a_full, a_par); a_par ^= 1;
                 tc_fence_after();
                 for (int n = g; n < N_v; n += groups, ++tile) {
                     const uint32_t buf = tile & 1u, use = tile >> 1;
+                    AVT_TRACE(t0 = clock64();)
                     mbar_wait(&tmem_empty[buf], (use & 1u) ^ 1u);
+                    AVT_TRACE(tw_empty += clock64() - t0;)
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + buf * kAccCols;
-                    for (int kc = 0; kc < KC; ++kc) {
+                    // descriptors differ only in their 14-bit address field (bytes >> 4): one add each
+                    uint64_t a_desc = a_desc0;
+                    for (int kc = 0; kc < KC; ++kc, a_desc += (uint64_t)(kABytes >> 4)) {
+                        AVT_TRACE(t0 = clock64();)
                         mbar_wait(&full_b[stage], phase);
+                        AVT_TRACE(tw_full += clock64() - t0;)
                         tc_fence_after();
-                        const uint32_t a_addr = smem_u32(sA + (size_t)kc * kABytes);
-                        const uint32_t b_addr = smem_u32(sB + (size_t)stage * kStageBytes);
+                        const uint64_t b_desc = b_desc0 + (uint64_t)((uint32_t)stage * (uint32_t)(kStageBytes >> 4));
+                        if (elect_one()) {
 #pragma unroll
-                        for (int k = 0; k < kBK / 16; ++k) {
-                            const uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
-                            const uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
-                            if (kPair) umma2_f16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
-                            else umma_f16_ss(d_tmem, ad, bd, idesc, (uint32_t)((kc | k) != 0));
+                            for (int k = 0; k < kBK / 16; ++k) {
+                                if (kPair) umma2_f16_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (uint32_t)((kc | k) != 0));
+                                else umma_f16_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (uint32_t)((kc | k) != 0));
+                            }
+                            // frees the stage (in both CTAs) once these MMAs retire
+                            if (kPair) umma2_commit_mc(&empty_b[stage], 3); else umma_commit(&empty_b[stage]);
                         }
-                        // frees the stage (in both CTAs) once these MMAs retire
-                        if (kPair) umma2_commit_mc(&empty_b[stage], 3); else umma_commit(&empty_b[stage]);
+                        __syncwarp();
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
-                    if (kPair) umma2_commit_mc(&tmem_full[buf], 3); else umma_commit(&tmem_full[buf]);
+                    if (elect_one()) { if (kPair) umma2_commit_mc(&tmem_full[buf], 3); else umma_commit(&tmem_full[buf]); }
+                    __syncwarp();
                 }
-                if (kPair) umma2_commit_mc(a_empty, 3); else umma_commit(a_empty);
+                if (elect_one()) { if (kPair) umma2_commit_mc(a_empty, 3); else umma_commit(a_empty); }
+                __syncwarp();
             }
+            AVT_TRACE(if (lane == 0) { g_tc_trace[blockIdx.x * 8 + 0] = tw_full; g_tc_trace[blockIdx.x * 8 + 1] = tw_empty;
+                      g_tc_trace[blockIdx.x * 8 + 2] = clock64() - t_begin; g_tc_trace[blockIdx.x * 8 + 6] = tile; })
         }
-    } else {                                             // ---------------- epilogue warps 2 .. 2 + kEpiWarps
+    } else {                                             // ---------------- epilogue warps 0 .. kEpiWarps-1
         // kColGroups warps per TMEM lane quarter (one per scheduler each): every warp takes a slice of
         // the image's positions, so each SM sub-partition has four warps to hide MUFU / TMEM latency
         // (ncu of the 2-group version: issue slots 50 % busy, tensor pipe 46 % -- latency-bound)
         const int q = warp & 3;                          // TMEM lane quarter this warp may touch
-        const int grp = (warp - 2) >> 2;                 // column group 0 .. kColGroups-1
+        const int grp = warp >> 2;                 // column group 0 .. kColGroups-1
         const int cw = ((P / kColGroups) >> 4) << 4;     // 48 for P = 196; the last group takes the rest
         const int c_begin = grp * cw, c_end = (grp == kColGroups - 1) ? P : (grp + 1) * cw;
         const int row = q * 32 + lane;
@@ -286,6 +317,7 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
         // by the two contractions that consume them
         const float gscale = kGrad ? pow2i(g_scale_exp(__ldg(gmax_bits))) : 1.0f;
         uint32_t tile = 0;
+        AVT_TRACE(long long te_wait = 0; long long te_sweep = 0; const long long te_begin = clock64(); long long e0;)
         for (int u = u0; u < n_ut; u += u_step) {
             const int mt = kPair ? 2 * u + (int)rank : u;
             const int k = mt * kBM + row;
@@ -317,7 +349,9 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                 }
                 __half* gout = G + (size_t)n * P * n_a_pad + k;
                 const uint32_t pitch = (uint32_t)n_a_pad;
+                AVT_TRACE(e0 = clock64();)
                 mbar_wait(&tmem_full[buf], use & 1u);
+                AVT_TRACE(te_wait += clock64() - e0; e0 = clock64();)
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kAccCols;
                 float num = 0.f, dn = 0.f;
@@ -328,6 +362,7 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                 else cell_sweep<kGrad, false, kPitch>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
                 if (!kGrad && __any_sync(0xffffffffu, !(dn >= kTinyFwd * (float)(c_end - c_begin))))
                     cell_sweep<false, true, 0>(taddr, c_begin, c_end, cx, num, dn, gout, pitch);
+                AVT_TRACE(te_sweep += clock64() - e0;)
                 tc_fence_before();
                 // accumulator may be overwritten (pair: the leader's barrier collects both CTAs)
                 if (!kPair || rank == 0) mbar_arrive(&tmem_empty[buf]); else mbar_arrive_leader(&tmem_empty[buf]);
@@ -363,11 +398,13 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                 }
             }
         }
+        AVT_TRACE(if (warp == 0 && lane == 0) { g_tc_trace[blockIdx.x * 8 + 3] = te_wait; g_tc_trace[blockIdx.x * 8 + 4] = te_sweep;
+                                                g_tc_trace[blockIdx.x * 8 + 5] = clock64() - te_begin; })
     }
     tc_fence_before();
     __syncthreads();
     if (kPair) cluster_sync();                           // nobody leaves while the pair may still touch its smem / TMEM
-    if (warp == 1) {
+    if (warp == kWarpMma) {
         tc_fence_after();
         if (kPair) tmem_dealloc2(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols);
     }
@@ -463,3 +500,9 @@ int launch_grad_cells_f16(const __half* vt, const __half* a_h, const int32_t* po
 }
 
 }  // namespace avt
+
+#ifdef AVT_TC_TRACE
+extern "C" int avt_debug_tc_trace(unsigned long long* host_out, int n_blocks) {
+    return cudaMemcpyFromSymbol(host_out, avt::g_tc_trace, sizeof(unsigned long long) * 8 * (size_t)n_blocks) == cudaSuccess ? 0 : -2;
+}
+#endif

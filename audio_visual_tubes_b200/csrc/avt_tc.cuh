@@ -14,6 +14,18 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One lane of a converged warp (always the same one for a full mask).  The MMA-issuing warps run
+// their loops WARP-UNIFORMLY and elect a lane only around the tcgen05.mma / commit instructions: inside
+// an `if (lane == 0)` region the compiler keeps descriptors and barrier addresses in vector registers
+// and pays an R2UR per operand of every UTCHMMA, and that single thread's instruction stream -- not the
+// tensor pipe -- bounded the MMA rate (probe: 104 -> 126..144 clocks per MMA with a few extra
+// instructions in the issue loop; scripts/probes/mma_probe2.cu).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 // ------------------------------------------------------------------ mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
