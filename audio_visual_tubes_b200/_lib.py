@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libavtubes.so")
+# AVT_LIB_PATH: development only -- load an experimental build (scripts/build_variant.sh) instead
+LIB_PATH = os.environ.get("AVT_LIB_PATH") or os.path.join(HERE, "libavtubes.so")
 
 PRECISION_FP32 = 0
 PRECISION_F16 = 1

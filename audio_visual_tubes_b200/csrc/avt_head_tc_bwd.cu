@@ -16,6 +16,11 @@
 #include <mutex>
 #include "avt_tc.cuh"
 #include <stdlib.h>
+#ifdef AVT_DV_PLAIN_STORE
+#define AVT_DV_ST(p, x) (*(p) = (x))
+#else
+#define AVT_DV_ST(p, x) __stcs((p), (x))
+#endif
 
 namespace avt {
 using namespace tc;
@@ -373,8 +378,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     if (valid) {
 #pragma unroll
                         for (int e = 0; e < 16; ++e) {
-                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-h_lo(xa[j][e]), rt, rn * __uint_as_float(r[2 * e])));
-                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-h_hi(xa[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
+                            AVT_DV_ST(o + (uint32_t)(2 * e) * Pu, fmaf(-h_lo(xa[j][e]), rt, rn * __uint_as_float(r[2 * e])));
+                            AVT_DV_ST(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-h_hi(xa[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
                         }
                     }
                 }
@@ -392,8 +397,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     if (valid) {
 #pragma unroll
                         for (int e = 0; e < 16; ++e) {
-                            __stcs(o + (uint32_t)(2 * e) * Pu, fmaf(-h_lo(xb[j][e]), rt, rn * __uint_as_float(r[2 * e])));
-                            __stcs(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-h_hi(xb[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
+                            AVT_DV_ST(o + (uint32_t)(2 * e) * Pu, fmaf(-h_lo(xb[j][e]), rt, rn * __uint_as_float(r[2 * e])));
+                            AVT_DV_ST(o + (uint32_t)(2 * e + 1) * Pu, fmaf(-h_hi(xb[j][e]), rt, rn * __uint_as_float(r[2 * e + 1])));
                         }
                     }
                 }
@@ -599,7 +604,11 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             }
         }
     } else if (warp == kDaWarpMma) {
+#ifdef AVT_DA_LANE0
+        if (rank == 0 && lane == 0) {
+#else
         if (rank == 0) {                                 // ---------------- MMA issuer (leader only; warp-uniform loop)
+#endif
             const uint32_t idesc = make_idesc_f16(256, 256, 1, 1);
             const uint64_t desc0 = make_smem_desc(smem_u32(stages), kDa2BlockBytes, 1024);
             int stage = 0; uint32_t phase = 0;

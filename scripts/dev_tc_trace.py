@@ -30,3 +30,4 @@ dump("forward ")
 for _ in range(2):
     dv, da = head_backward_raw(v, ah, cfg, out, 0.0, rowgrad_done=True)
 dump("backward")
+
