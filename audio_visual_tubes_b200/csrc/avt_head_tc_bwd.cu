@@ -221,12 +221,18 @@ bwd_dv_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__
 constexpr int kDv2BHalfBytes = 128 * kDvBK * 2;       // this CTA's 128 channel rows of one N = 256 MMA
 constexpr int kDv2StageBytes = kDvABytes + kDv2BHalfBytes;         // 32 KB
 constexpr int kDv2Stages = 6;
-constexpr size_t kDv2SmemBytes = 1024 + (size_t)kDv2Stages * kDv2StageBytes + 256 + 2 * 2 * kDvBM * 4;
+constexpr size_t kDv2SmemBytes = 1024 + (size_t)kDv2Stages * kDv2StageBytes + 256 + 2 * 4 * kDvBM * 4;
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kDvThreads, 1)
+// kG = column groups per half of C (epilogue warps = 4 * kG): 2 -> 8 warps of 128 columns per half,
+// 4 -> 16 warps of 64 columns (twice the warps per scheduler to hide TMEM / store latency)
+// kP: compile-time P (196 = the reference's 14 x 14 maps; 0 = run time) so that the 256 strided NCHW
+// stores of a thread are STG [base + immediate] (with a run-time P every store paid an address
+// computation and the kernel spilled 400 bytes)
+template <int kG, int kP>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 128 * kG, 1)
 bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_at,
                    const __half* __restrict__ vt, const float* __restrict__ rnorm_v,
-                   float* __restrict__ dv, int n_rows, int n_tile_pairs, int KC, int C, int P,
+                   float* __restrict__ dv, int n_rows, int n_tile_pairs, int KC, int C, int P_rt,
                    const unsigned int* __restrict__ gmax_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -237,28 +243,33 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
     uint64_t* tmem_full = bars + 2 * kDv2Stages;         // [2] one per half of C
     uint64_t* tmem_empty = tmem_full + 2;                // [2] leader's copies: 256 local + 256 peer arrivals
     uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-    float* t_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][2][128]
+    float* t_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][kG][128]
+    constexpr int kWTma = 4 * kG, kWMma = 4 * kG + 1;     // the two single-thread roles keep the highest warp ids
+    constexpr int kCW = 256 / kG;                          // columns of one thread per half
+    constexpr int kJ = kCW / 32;                           // 32-column chunks per thread and half
+    constexpr uint32_t kEpiThreads = 128u * kG;
 
+    const int P = kP ? kP : P_rt;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const int pair0 = blockIdx.x >> 1, pair_step = gridDim.x >> 1;
     const int nh = C / 256;                              // C is 256 or 512
 
-    if (warp == kDvWarpTma && lane == 0) {
+    if (warp == kWTma && lane == 0) {
         prefetch_tmap(&map_g);
         prefetch_tmap(&map_at);
         for (int i = 0; i < kDv2Stages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 512); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 2 * kEpiThreads); }
         fence_barrier_init();
     }
-    if (warp == kDvWarpMma) tmem_alloc2(tmem_holder, 512);
+    if (warp == kWMma) tmem_alloc2(tmem_holder, 512);
     tc_fence_before();
     __syncthreads();
     cluster_sync();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_holder;
 
-    if (warp == kDvWarpTma) {
+    if (warp == kWTma) {
         if (lane == 0) {                                 // ---------------- TMA producer (both CTAs)
             int stage = 0; uint32_t phase = 0;
             for (int tp = pair0; tp < n_tile_pairs; tp += pair_step) {
@@ -276,7 +287,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 }
             }
         }
-    } else if (warp == kDvWarpMma) {
+    } else if (warp == kWMma) {
         if (rank == 0) {                                 // ---------------- MMA issuer (leader only; warp-uniform
             const uint32_t idesc = make_idesc_f16(256, 256, 0, 0);               // loop, one elected lane issues)
             const uint64_t desc0 = make_smem_desc(smem_u32(stages), 16, 1024);
@@ -305,7 +316,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 }
             }
         }
-    } else {                                             // ---------------- epilogue warps 0..7
+    } else {                                             // ---------------- epilogue warps 0 .. 4*kG-1
         const int q = warp & 3;
         const int grp = warp >> 2;
         const int r_in = q * 32 + lane;
@@ -322,19 +333,19 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             // v_hat row pieces are fetched ahead of their use: the first half before the
             // accumulator is even ready, the second while the first is being reduced, and the
             // second pass starts with the half that is still in registers.
-            uint32_t xa[4][16], xb[4][16];
-            const int ca = grp * 128, cb = 256 + grp * 128;        // this thread's columns of h = 0 / 1
+            uint32_t xa[kJ][16], xb[kJ][16];
+            const int ca = grp * kCW, cb = 256 + grp * kCW;        // this thread's columns of h = 0 / 1
 #pragma unroll
-            for (int j = 0; j < 4; ++j) { ld_nc_v8(vrow + ca + 32 * j, xa[j]); ld_nc_v8(vrow + ca + 32 * j + 16, xa[j] + 8); }
+            for (int j = 0; j < kJ; ++j) { ld_nc_v8(vrow + ca + 32 * j, xa[j]); ld_nc_v8(vrow + ca + 32 * j + 16, xa[j] + 8); }
             if (nh == 2) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) { ld_nc_v8(vrow + cb + 32 * j, xb[j]); ld_nc_v8(vrow + cb + 32 * j + 16, xb[j] + 8); }
+                for (int j = 0; j < kJ; ++j) { ld_nc_v8(vrow + cb + 32 * j, xb[j]); ld_nc_v8(vrow + cb + 32 * j + 16, xb[j] + 8); }
             }
             mbar_wait(&tmem_full[0], it & 1u);
             tc_fence_after();
             float t = 0.f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kJ; ++j) {
                 uint32_t r[32];
                 tmem_ld_32x32(lane_addr + (uint32_t)(ca + 32 * j), r);
                 tmem_ld_wait();
@@ -348,7 +359,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 mbar_wait(&tmem_full[1], it & 1u);
                 tc_fence_after();
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < kJ; ++j) {
                     uint32_t r[32];
                     tmem_ld_32x32(lane_addr + (uint32_t)(cb + 32 * j), r);
                     tmem_ld_wait();
@@ -359,10 +370,12 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     }
                 }
             }
-            float* tpart = t_part + (it & 1u) * 2 * kDvBM;
+            float* tpart = t_part + (it & 1u) * kG * kDvBM;
             tpart[grp * kDvBM + r_in] = t;
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            t = tpart[r_in] + tpart[kDvBM + r_in];
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+            t = 0.f;
+#pragma unroll
+            for (int j = 0; j < kG; ++j) t += tpart[j * kDvBM + r_in];
             const float rn = rnorm_v[rowc] * pow2i(-g_scale_exp(__ldg(gmax_bits)));   // undo the scale of G
             const float rt = rn * t;
             // pass 2: dv = rn * dv_hat - (rn t) * v_hat, NCHW fp32; each half is released as soon
@@ -370,7 +383,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             {
                 float* obase = dv + ((size_t)n * C + ca) * P + p;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < kJ; ++j) {
                     uint32_t r[32];
                     tmem_ld_32x32(lane_addr + (uint32_t)(ca + 32 * j), r);
                     tmem_ld_wait();
@@ -389,7 +402,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             if (nh == 2) {
                 float* obase = dv + ((size_t)n * C + cb) * P + p;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < kJ; ++j) {
                     uint32_t r[32];
                     tmem_ld_32x32(lane_addr + (uint32_t)(cb + 32 * j), r);
                     tmem_ld_wait();
@@ -410,7 +423,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
     tc_fence_before();
     __syncthreads();
     cluster_sync();
-    if (warp == kDvWarpMma) {
+    if (warp == kWMma) {
         tc_fence_after();
         tmem_dealloc2(tmem_base, 512);
     }
@@ -711,9 +724,10 @@ static SideStream* side_stream(int dev, cudaStream_t owner) {
 }
 
 // AVT_NO_SIDE_STREAM / AVT_NO_PAIR are development switches: read ONCE per process
-struct EnvSwitches { bool no_side, no_pair; };
+struct EnvSwitches { bool no_side, no_pair; int dv_groups; };
 static const EnvSwitches& env_switches() {
-    static const EnvSwitches e{getenv("AVT_NO_SIDE_STREAM") != nullptr, getenv("AVT_NO_PAIR") != nullptr};
+    static const EnvSwitches e{getenv("AVT_NO_SIDE_STREAM") != nullptr, getenv("AVT_NO_PAIR") != nullptr,
+                                 getenv("AVT_DV_GROUPS") ? atoi(getenv("AVT_DV_GROUPS")) : 2};
     return e;
 }
 
@@ -790,10 +804,16 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
         if (pair) {
             const int n_pairs = (n_tiles + 1) / 2;
             const int grid_pairs = n_pairs < sms / 2 ? n_pairs : sms / 2;
-            AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                (int)kDv2SmemBytes));
-            bwd_dv_pair_kernel<<<2 * grid_pairs, kDvThreads, kDv2SmemBytes, st_dv>>>(map_g, map_at, vt, rnorm_v, dv,
-                                                                                  n_rows, n_pairs, n_a_pad / kDvBK, C, P, gmax_bits);
+#define AVT_DV(G, PP)                                                                                          \
+    do {                                                                                                       \
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_pair_kernel<G, PP>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                            (int)kDv2SmemBytes));                                              \
+        bwd_dv_pair_kernel<G, PP><<<2 * grid_pairs, 64 + 128 * G, kDv2SmemBytes, st_dv>>>(                       \
+            map_g, map_at, vt, rnorm_v, dv, n_rows, n_pairs, n_a_pad / kDvBK, C, P, gmax_bits);                \
+    } while (0)
+            if (env.dv_groups == 4) { if (P == 196) AVT_DV(4, 196); else AVT_DV(4, 0); }
+            else { if (P == 196) AVT_DV(2, 196); else AVT_DV(2, 0); }
+#undef AVT_DV
         } else {
             const int grid = n_tiles < sms ? n_tiles : sms;
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
