@@ -25,6 +25,16 @@
 namespace avt {
 using namespace tc;
 
+#ifdef AVT_TC_TRACE
+// development build only: per-block cycle counters of the dv kernel -- [0] issuer waiting for operands,
+// [1] issuer waiting for a free accumulator half, [2] issuer total, [3] epilogue waiting for accumulators,
+// [4] epilogue pass 1 (t), [5] epilogue total, [6] tiles, [7] epilogue pass 2 (stores)
+__device__ unsigned long long g_dv_trace[1024 * 8];
+#define AVT_TRACE(x) x
+#else
+#define AVT_TRACE(x)
+#endif
+
 // ------------------------------------------------------------------ a_hat^T (fp16)
 __global__ void transpose_audio_kernel(const __half* __restrict__ a_h, int n_a_pad, int C,
                                        __half* __restrict__ at_h) {
@@ -292,13 +302,18 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             const uint32_t idesc = make_idesc_f16(256, 256, 0, 0);               // loop, one elected lane issues)
             const uint64_t desc0 = make_smem_desc(smem_u32(stages), 16, 1024);
             int stage = 0; uint32_t phase = 0, it = 0;
+            AVT_TRACE(long long tw_full = 0; long long tw_empty = 0; const long long t_begin = clock64(); long long t0;)
             for (int tp = pair0; tp < n_tile_pairs; tp += pair_step, ++it) {
                 for (int h = 0; h < nh; ++h) {
+                    AVT_TRACE(t0 = clock64();)
                     mbar_wait(&tmem_empty[h], (it & 1u) ^ 1u);
+                    AVT_TRACE(tw_empty += clock64() - t0;)
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + (uint32_t)h * 256u;
                     for (int kc = 0; kc < KC; ++kc) {
+                        AVT_TRACE(t0 = clock64();)
                         mbar_wait(&full_b[stage], phase);
+                        AVT_TRACE(tw_full += clock64() - t0;)
                         tc_fence_after();
                         const uint64_t ad = desc0 + (uint64_t)((uint32_t)stage * (uint32_t)(kDv2StageBytes >> 4));
                         const uint64_t bd = ad + (uint64_t)(kDvABytes >> 4);
@@ -315,6 +330,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                     __syncwarp();
                 }
             }
+            AVT_TRACE(if (lane == 0) { g_dv_trace[blockIdx.x * 8 + 0] = tw_full; g_dv_trace[blockIdx.x * 8 + 1] = tw_empty;
+                      g_dv_trace[blockIdx.x * 8 + 2] = clock64() - t_begin; g_dv_trace[blockIdx.x * 8 + 6] = it; })
         }
     } else {                                             // ---------------- epilogue warps 0 .. 4*kG-1
         const int q = warp & 3;
@@ -322,6 +339,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
         const int r_in = q * 32 + lane;
         const uint32_t Pu = (uint32_t)P;
         uint32_t it = 0;
+        AVT_TRACE(long long te_wait = 0; long long te_p1 = 0; long long te_p2 = 0; const long long te_begin = clock64(); long long e0;)
         for (int tp = pair0; tp < n_tile_pairs; tp += pair_step, ++it) {
             const int row = (tp * 2 + (int)rank) * kDvBM + r_in;
             const bool valid = row < n_rows;
@@ -341,7 +359,9 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
 #pragma unroll
                 for (int j = 0; j < kJ; ++j) { ld_nc_v8(vrow + cb + 32 * j, xb[j]); ld_nc_v8(vrow + cb + 32 * j + 16, xb[j] + 8); }
             }
+            AVT_TRACE(e0 = clock64();)
             mbar_wait(&tmem_full[0], it & 1u);
+            AVT_TRACE(te_wait += clock64() - e0; e0 = clock64();)
             tc_fence_after();
             float t = 0.f;
 #pragma unroll
@@ -356,7 +376,9 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 }
             }
             if (nh == 2) {
+                AVT_TRACE(te_p1 += clock64() - e0; e0 = clock64();)
                 mbar_wait(&tmem_full[1], it & 1u);
+                AVT_TRACE(te_wait += clock64() - e0; e0 = clock64();)
                 tc_fence_after();
 #pragma unroll
                 for (int j = 0; j < kJ; ++j) {
@@ -378,6 +400,7 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
             for (int j = 0; j < kG; ++j) t += tpart[j * kDvBM + r_in];
             const float rn = rnorm_v[rowc] * pow2i(-g_scale_exp(__ldg(gmax_bits)));   // undo the scale of G
             const float rt = rn * t;
+            AVT_TRACE(te_p1 += clock64() - e0; e0 = clock64();)
             // pass 2: dv = rn * dv_hat - (rn t) * v_hat, NCHW fp32; each half is released as soon
             // as it has been written so the next tile's MMAs can start on it
             {
@@ -418,7 +441,10 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 tc_fence_before();
                 if (rank == 0) mbar_arrive(&tmem_empty[1]); else mbar_arrive_leader(&tmem_empty[1]);
             }
+            AVT_TRACE(te_p2 += clock64() - e0;)
         }
+        AVT_TRACE(if (warp == 0 && lane == 0) { g_dv_trace[blockIdx.x * 8 + 3] = te_wait; g_dv_trace[blockIdx.x * 8 + 4] = te_p1;
+                                                g_dv_trace[blockIdx.x * 8 + 5] = clock64() - te_begin; g_dv_trace[blockIdx.x * 8 + 7] = te_p2; })
     }
     tc_fence_before();
     __syncthreads();
@@ -863,3 +889,9 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
 }
 
 }  // namespace avt
+
+#ifdef AVT_TC_TRACE
+extern "C" int avt_debug_dv_trace(unsigned long long* host_out, int n_blocks) {
+    return cudaMemcpyFromSymbol(host_out, avt::g_dv_trace, sizeof(unsigned long long) * 8 * (size_t)n_blocks) == cudaSuccess ? 0 : -2;
+}
+#endif

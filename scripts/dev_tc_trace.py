@@ -31,3 +31,24 @@ for _ in range(2):
     dv, da = head_backward_raw(v, ah, cfg, out, 0.0, rowgrad_done=True)
 dump("backward")
 
+
+def dump_dv():
+    torch.cuda.synchronize()
+    buf = (ctypes.c_ulonglong * (8 * 148))()
+    assert lib.avt_debug_dv_trace(buf, 148) == 0
+    t = np.array(buf, dtype=np.float64).reshape(148, 8)
+    lead = t[t[:, 2] > 0]
+    tiles = lead[:, 6].mean()
+    print("dv: blocks with an issuer:", len(lead), "tile pairs/block", tiles)
+    print("  issuer: total %.0f  wait operands %.0f (%.1f%%)  wait accumulator %.0f (%.1f%%)  per tile %.0f clk" % (
+        lead[:, 2].mean(), lead[:, 0].mean(), 100 * lead[:, 0].mean() / lead[:, 2].mean(), lead[:, 1].mean(),
+        100 * lead[:, 1].mean() / lead[:, 2].mean(), lead[:, 2].mean() / tiles))
+    e = t[t[:, 5] > 0]
+    print("  epilogue warp 0: total %.0f  wait accumulators %.0f (%.1f%%)  pass 1 %.0f (%.1f%%)  pass 2 %.0f (%.1f%%)  per tile: wait %.0f p1 %.0f p2 %.0f" % (
+        e[:, 5].mean(), e[:, 3].mean(), 100 * e[:, 3].mean() / e[:, 5].mean(), e[:, 4].mean(), 100 * e[:, 4].mean() / e[:, 5].mean(),
+        e[:, 7].mean(), 100 * e[:, 7].mean() / e[:, 5].mean(), e[:, 3].mean() / tiles, e[:, 4].mean() / tiles, e[:, 7].mean() / tiles))
+
+
+if hasattr(lib, "avt_debug_dv_trace"):
+    dump_dv()
+
