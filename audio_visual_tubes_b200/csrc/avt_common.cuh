@@ -163,6 +163,6 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h, __half* 
                     const float* GA, float* dv, float* d_ahat, const unsigned int* gmax_bits,
                     cudaStream_t dv_stream, cudaStream_t st);
 int launch_audio_to_f16(const float* a_hat, int N_a, int N_a_pad, int C, __half* out,
-                         cudaStream_t st);
+                         unsigned int* zero_word, cudaStream_t st);
 
 }  // namespace avt

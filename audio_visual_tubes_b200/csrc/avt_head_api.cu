@@ -116,7 +116,7 @@ extern "C" int avt_head_forward(const void* v_any, int v_dtype, const float* a_h
     } else {
         __half* a_h = reinterpret_cast<__half*>(ws + w.a_h);
         const int n_a_pad = n_a_padded(N_a);
-        rc = launch_audio_to_f16(a_hat, N_a, n_a_pad, C, a_h, st);
+        rc = launch_audio_to_f16(a_hat, N_a, n_a_pad, C, a_h, fuse ? &scratch->gmax_bits : nullptr, st);
         if (rc != AVT_OK) return rc;
         rc = launch_sim_f16(vt, a_h, pos_idx, col_offset, N_v, N_a, C, P, hp, logits, sim, den, st);
         if (rc != AVT_OK) return rc;
@@ -125,10 +125,7 @@ extern "C" int avt_head_forward(const void* v_any, int v_dtype, const float* a_h
     if (fuse) {             // fused training step: the row gradients come out of the finish kernel
         gsim = reinterpret_cast<float*>(ws + w.gsim);
         GA = reinterpret_cast<float*>(ws + w.ga);
-        if (precision == AVT_PRECISION_F16) {
-            gmax_bits = &scratch->gmax_bits;
-            AVT_CHECK_CUDA(cudaMemsetAsync(gmax_bits, 0, sizeof(unsigned int), st));
-        }
+        if (precision == AVT_PRECISION_F16) gmax_bits = &scratch->gmax_bits;    // zeroed by the audio operand kernel
     }
     return launch_finish_rows(A, msum, N_v, N_a, P, hp, Pos, Neg, weighted_A, logits, loss_rows,
                               loss_sum, scratch, pos_idx, col_offset, sim, col_mult, fuse_grad_scale, gsim, GA,

@@ -40,9 +40,12 @@ __global__ void audio_normalize_bwd_kernel(const float* __restrict__ a_hat,
     for (int c = lane; c < C; c += 32) da[(size_t)row * C + c] = rn * (g[c] - h[c] * dot);
 }
 
+// also zeroes *zero_word (the bound of the cell gradients that the fused row-finish kernel max-reduces
+// into): one memset node less between the contraction and the row kernel
 __global__ void audio_to_f16_kernel(const float* __restrict__ a_hat, int N_a, int N_a_pad, int C,
-                                     __half* __restrict__ out) {
+                                     __half* __restrict__ out, unsigned int* __restrict__ zero_word) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0 && zero_word) *zero_word = 0u;
     size_t total = (size_t)N_a_pad * C;
     if (i >= total) return;
     size_t row = i / C;
@@ -50,9 +53,9 @@ __global__ void audio_to_f16_kernel(const float* __restrict__ a_hat, int N_a, in
 }
 
 int launch_audio_to_f16(const float* a_hat, int N_a, int N_a_pad, int C, __half* out,
-                         cudaStream_t st) {
+                         unsigned int* zero_word, cudaStream_t st) {
     size_t total = (size_t)N_a_pad * C;
-    audio_to_f16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(a_hat, N_a, N_a_pad, C, out);
+    audio_to_f16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(a_hat, N_a, N_a_pad, C, out, zero_word);
     AVT_LAUNCH_CHECK();
     return AVT_OK;
 }

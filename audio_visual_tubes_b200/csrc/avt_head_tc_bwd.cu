@@ -238,11 +238,14 @@ constexpr size_t kDv2SmemBytes = 1024 + (size_t)kDv2Stages * kDv2StageBytes + 25
 // kP: compile-time P (196 = the reference's 14 x 14 maps; 0 = run time) so that the 256 strided NCHW
 // stores of a thread are STG [base + immediate] (with a run-time P every store paid an address
 // computation and the kernel spilled 400 bytes)
-template <int kG, int kP>
+// kBmn: the B operand is a_hat itself, [k][c] row-major = MN-major (N = c contiguous), fetched as two
+// [64 k][64 c] SW128 blocks per CTA exactly like the d_ahat kernel's operands -- no transposed copy of
+// the audio rows, no transpose launch.  false: K-major rows of a_hat^T (the first version; A/B switch).
+template <int kG, int kP, bool kBmn>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 128 * kG, 1)
 bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_at,
                    const __half* __restrict__ vt, const float* __restrict__ rnorm_v,
-                   float* __restrict__ dv, int n_rows, int n_tile_pairs, int KC, int C, int P_rt,
+                   float* __restrict__ dv, int n_rows, int n_tile_pairs, int KC, int C, int P_rt, int reverse,
                    const unsigned int* __restrict__ gmax_bits) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -282,7 +285,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
     if (warp == kWTma) {
         if (lane == 0) {                                 // ---------------- TMA producer (both CTAs)
             int stage = 0; uint32_t phase = 0;
-            for (int tp = pair0; tp < n_tile_pairs; tp += pair_step) {
+            for (int ti = pair0; ti < n_tile_pairs; ti += pair_step) {
+                const int tp = reverse ? n_tile_pairs - 1 - ti : ti;
                 const int tile = tp * 2 + (int)rank;
                 for (int h = 0; h < nh; ++h) {
                     for (int kc = 0; kc < KC; ++kc) {
@@ -290,8 +294,10 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                         if (rank == 0) mbar_arrive_expect_tx(&full_b[stage], (uint32_t)(2 * kDv2StageBytes));
                         uint8_t* sA = stages + (size_t)stage * kDv2StageBytes;
                         tma_load_2d_pair(sA, &map_g, &full_b[stage], kc * kDvBK, tile * kDvBM);
-                        tma_load_2d_pair(sA + kDvABytes, &map_at, &full_b[stage], kc * kDvBK,
-                                         h * 256 + (int)rank * 128);
+                        if (kBmn) tma_load_3d_pair(sA + kDvABytes, &map_at, &full_b[stage], 0, kc * kDvBK,
+                                                   h * 4 + (int)rank * 2);
+                        else tma_load_2d_pair(sA + kDvABytes, &map_at, &full_b[stage], kc * kDvBK,
+                                              h * 256 + (int)rank * 128);
                         if (++stage == kDv2Stages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -299,11 +305,15 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
         }
     } else if (warp == kWMma) {
         if (rank == 0) {                                 // ---------------- MMA issuer (leader only; warp-uniform
-            const uint32_t idesc = make_idesc_f16(256, 256, 0, 0);               // loop, one elected lane issues)
+            const uint32_t idesc = make_idesc_f16(256, 256, 0, kBmn ? 1 : 0);   // loop, one elected lane issues)
             const uint64_t desc0 = make_smem_desc(smem_u32(stages), 16, 1024);
+            // MN-major B: 64-channel blocks one LBO (8 KB) apart, 8 k rows per 1024 B; 16 k rows = 2048 B
+            const uint64_t bdesc0 = kBmn ? make_smem_desc(smem_u32(stages) + kDvABytes, 64 * 128, 1024)
+                                         : desc0 + (uint64_t)(kDvABytes >> 4);
+            constexpr uint32_t kBStep = kBmn ? (2048u >> 4) : 2u;
             int stage = 0; uint32_t phase = 0, it = 0;
             AVT_TRACE(long long tw_full = 0; long long tw_empty = 0; const long long t_begin = clock64(); long long t0;)
-            for (int tp = pair0; tp < n_tile_pairs; tp += pair_step, ++it) {
+            for (int ti = pair0; ti < n_tile_pairs; ti += pair_step, ++it) {
                 for (int h = 0; h < nh; ++h) {
                     AVT_TRACE(t0 = clock64();)
                     mbar_wait(&tmem_empty[h], (it & 1u) ^ 1u);
@@ -316,11 +326,11 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                         AVT_TRACE(tw_full += clock64() - t0;)
                         tc_fence_after();
                         const uint64_t ad = desc0 + (uint64_t)((uint32_t)stage * (uint32_t)(kDv2StageBytes >> 4));
-                        const uint64_t bd = ad + (uint64_t)(kDvABytes >> 4);
+                        const uint64_t bd = bdesc0 + (uint64_t)((uint32_t)stage * (uint32_t)(kDv2StageBytes >> 4));
                         if (elect_one()) {
 #pragma unroll
                             for (int k = 0; k < kDvBK / 16; ++k)
-                                umma2_f16_ss(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)((kc | k) != 0));
+                                umma2_f16_ss(d_tmem, ad + 2 * k, bd + kBStep * k, idesc, (uint32_t)((kc | k) != 0));
                             umma2_commit_mc(&empty_b[stage], 3);
                         }
                         __syncwarp();
@@ -340,7 +350,8 @@ bwd_dv_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
         const uint32_t Pu = (uint32_t)P;
         uint32_t it = 0;
         AVT_TRACE(long long te_wait = 0; long long te_p1 = 0; long long te_p2 = 0; const long long te_begin = clock64(); long long e0;)
-        for (int tp = pair0; tp < n_tile_pairs; tp += pair_step, ++it) {
+        for (int ti = pair0; ti < n_tile_pairs; ti += pair_step, ++it) {
+            const int tp = reverse ? n_tile_pairs - 1 - ti : ti;
             const int row = (tp * 2 + (int)rank) * kDvBM + r_in;
             const bool valid = row < n_rows;
             const int rowc = row < n_rows ? row : n_rows - 1;
@@ -596,7 +607,7 @@ constexpr size_t kDa2SmemBytes = 1024 + (size_t)kDa2Stages * kDa2StageBytes + 25
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kDa2Threads, 1)
 bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_vt,
                    float* __restrict__ d_ahat, int N_a, int n_mt, int splits, int n_chunks, int C,
-                   const unsigned int* __restrict__ gmax_bits) {
+                   const unsigned int* __restrict__ gmax_bits, int order) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* stages = base;
@@ -609,8 +620,12 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const int mt = blockIdx.x % n_mt, split = blockIdx.x / n_mt;      // n_mt even: a pair shares `split`
-    const int ch0 = (int)((long long)split * n_chunks / splits);
-    const int ch1 = (int)((long long)(split + 1) * n_chunks / splits);
+    // order bit 0: chunks dealt round robin over the splits (all CTAs sweep the rows of G together, in step
+    // with a dv kernel running beside this one, so G and v_hat come from HBM once for both); bit 1: last rows first
+    const bool rr = (order & 1) != 0, rev = (order & 2) != 0;
+    const int ch0 = rr ? 0 : (int)((long long)split * n_chunks / splits);
+    const int ch1 = rr ? (n_chunks - split + splits - 1) / splits : (int)((long long)(split + 1) * n_chunks / splits);
+    auto chunk_of = [&](int i) -> int { const int c = rr ? split + i * splits : i; return rev ? n_chunks - 1 - c : c; };
     const int nh = C / 256;                  // C is 256 or 512
 
     if (warp == kDaWarpTma && lane == 0) {
@@ -635,10 +650,11 @@ bwd_da_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_const
                 if (rank == 0)                           // the leader's barrier counts both CTAs' bytes
                     mbar_arrive_expect_tx(&full_b[stage], (uint32_t)(2 * (kDa2ABytes + nh * kDa2BHalfBytes)));
                 uint8_t* sA = stages + (size_t)stage * kDa2StageBytes;
-                tma_load_3d_pair(sA, &map_g, &full_b[stage], 0, ch * kDa2BK, mt * 2);
+                const int row0 = chunk_of(ch) * kDa2BK;
+                tma_load_3d_pair(sA, &map_g, &full_b[stage], 0, row0, mt * 2);
                 for (int h = 0; h < nh; ++h)
                     tma_load_3d_pair(sA + kDa2ABytes + h * kDa2BHalfBytes, &map_vt, &full_b[stage], 0,
-                                     ch * kDa2BK, h * 4 + (int)rank * 2);
+                                     row0, h * 4 + (int)rank * 2);
                 if (++stage == kDa2Stages) { stage = 0; phase ^= 1; }
             }
         }
@@ -750,10 +766,14 @@ static SideStream* side_stream(int dev, cudaStream_t owner) {
 }
 
 // AVT_NO_SIDE_STREAM / AVT_NO_PAIR are development switches: read ONCE per process
-struct EnvSwitches { bool no_side, no_pair; int dv_groups; };
+struct EnvSwitches { bool no_side, no_pair; int dv_groups; bool dv_bt; int dv_pairs, da_splits; bool no_cosched; };
 static const EnvSwitches& env_switches() {
     static const EnvSwitches e{getenv("AVT_NO_SIDE_STREAM") != nullptr, getenv("AVT_NO_PAIR") != nullptr,
-                                 getenv("AVT_DV_GROUPS") ? atoi(getenv("AVT_DV_GROUPS")) : 2};
+                                 getenv("AVT_DV_GROUPS") ? atoi(getenv("AVT_DV_GROUPS")) : 2,
+                                 getenv("AVT_DV_BT") != nullptr,     // development: the first version's transposed-audio operand
+                                 getenv("AVT_DV_PAIRS") ? atoi(getenv("AVT_DV_PAIRS")) : 0,
+                                 getenv("AVT_DA_SPLITS") ? atoi(getenv("AVT_DA_SPLITS")) : 0,
+                                 getenv("AVT_NO_COSCHED") != nullptr};
     return e;
 }
 
@@ -789,56 +809,81 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
     // With stage profiling on, everything runs on `st` so that the stage times are those of the
     // kernels alone.
     const EnvSwitches& env = env_switches();
+    // the pair dv kernel reads a_hat itself as an MN-major operand; only the 1-CTA kernel (C other than
+    // 256 / 512) still wants the transposed copy
+    const bool dv_pair = (C == 256 || C == 512) && !env.no_pair;
+    const bool b_mn = dv_pair && !env.dv_bt;
     const bool serial = prof_enabled() || env.no_side;
+    // Co-scheduling.  The dv kernel alternates between a load phase (MMAs) and a store phase (its
+    // epilogue holds both accumulator halves: the Jacobian needs the whole row), so alone it keeps the
+    // tensor pipe 44 % and HBM 65 % busy; the d_ahat kernel is tensor-bound and reads the SAME G and
+    // v_hat.  Run side by side on disjoint SMs (5/8 of the SM pairs for dv, the rest for d_ahat), both
+    // sweeping the rows of G from the END (where the cell-gradient kernel has just left them in L2) and
+    // in step (d_ahat's K chunks dealt round robin over its splits), each fills the other's idle
+    // resource and G / v_hat come from HBM once for both: backward 637 -> 582 us at B = 1024,
+    // 120 -> 105 us for a 128-row shard (profiles/r2_ab_cosched.txt).
+    const bool cosched = dv_pair && !serial && !env.no_cosched;
+    const bool reverse = cosched;
     SideStream* side = serial ? nullptr : side_stream(dev, st);
     const bool ext = side && dv_stream && dv_stream != st;
     cudaStream_t st_dv = ext ? dv_stream : st;
     cudaStream_t st_da = (side && !ext) ? side->stream : st;
     cudaStream_t st_tr = ext ? dv_stream : st_da;        // stream of the audio transpose
     SideJoin joiner{ext ? nullptr : side, st};
-    if (side) {
-        AVT_CHECK_CUDA(cudaEventRecord(side->fork0, st));
-        AVT_CHECK_CUDA(cudaStreamWaitEvent(st_tr, side->fork0, 0));
-        joiner.forked = true;
-    }
-    {
+    if (!b_mn) {
+        if (side) {
+            AVT_CHECK_CUDA(cudaEventRecord(side->fork0, st));
+            AVT_CHECK_CUDA(cudaStreamWaitEvent(st_tr, side->fork0, 0));
+            joiner.forked = true;
+        }
         dim3 grid(n_a_pad / 32, C / 32), block(32, 8);
         transpose_audio_kernel<<<grid, block, 0, st_tr>>>(a_h, n_a_pad, C, at_h);
         AVT_LAUNCH_CHECK();
+        if (side && !ext) AVT_CHECK_CUDA(cudaEventRecord(side->tdone, side->stream));
     }
-    if (side && !ext) AVT_CHECK_CUDA(cudaEventRecord(side->tdone, side->stream));
     // stage 1: cell gradients
     int rc = launch_grad_cells_f16(vt, a_h, pos_idx, col_offset, N_v, N_a, n_a_pad, C, P, hp, sim, den,
                                     gsim, GA, g_h, gmax_bits, st);
     if (rc != AVT_OK) return rc;
     if (side) {
-        if (!ext) AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->tdone, 0));
+        if (!ext && !b_mn) AVT_CHECK_CUDA(cudaStreamWaitEvent(st, side->tdone, 0));
         AVT_CHECK_CUDA(cudaEventRecord(side->fork, st));
         AVT_CHECK_CUDA(cudaStreamWaitEvent(ext ? st_dv : side->stream, side->fork, 0));
+        joiner.forked = true;
     }
     // stage 2: dv
+    int dv_ctas = 0;
     {
         ProfScope _ps(kProfBwdDv, st_dv);
-        const bool pair = (C == 256 || C == 512) && !env.no_pair;
+        const bool pair = dv_pair;
         CUtensorMap map_g, map_at;
-        if (!make_tmap_f16_2d(&map_g, g_h, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, kDvBM) ||
-            !make_tmap_f16_2d(&map_at, at_h, (uint64_t)C, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, pair ? 128 : 256)) {
+        const bool ok_b = b_mn ? make_tmap_f16_blocks(&map_at, a_h, (uint64_t)n_a_pad, (uint64_t)C, (uint64_t)C * 2, kDvBK, 2)
+                               : make_tmap_f16_2d(&map_at, at_h, (uint64_t)C, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK,
+                                                  pair ? 128 : 256);
+        if (!make_tmap_f16_2d(&map_g, g_h, (uint64_t)n_rows, (uint64_t)n_a_pad, (uint64_t)n_a_pad * 2, kDvBK, kDvBM) || !ok_b) {
             set_error("fp16 backward: cuTensorMapEncodeTiled failed (dv)");
             return AVT_ERR_CUDA;
         }
         const int n_tiles = (n_rows + kDvBM - 1) / kDvBM;
         if (pair) {
             const int n_pairs = (n_tiles + 1) / 2;
-            const int grid_pairs = n_pairs < sms / 2 ? n_pairs : sms / 2;
-#define AVT_DV(G, PP)                                                                                          \
+            int grid_pairs = n_pairs < sms / 2 ? n_pairs : sms / 2;
+            if (cosched) {
+                const int want = env.dv_pairs > 0 ? env.dv_pairs : (sms / 2) * 5 / 8;
+                if (want >= 1 && want < grid_pairs) grid_pairs = want;
+            }
+            dv_ctas = 2 * grid_pairs;
+#define AVT_DV(G, PP, BM)                                                                                      \
     do {                                                                                                       \
-        AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_pair_kernel<G, PP>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+        AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_dv_pair_kernel<G, PP, BM>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                             (int)kDv2SmemBytes));                                              \
-        bwd_dv_pair_kernel<G, PP><<<2 * grid_pairs, 64 + 128 * G, kDv2SmemBytes, st_dv>>>(                       \
-            map_g, map_at, vt, rnorm_v, dv, n_rows, n_pairs, n_a_pad / kDvBK, C, P, gmax_bits);                \
+        bwd_dv_pair_kernel<G, PP, BM><<<2 * grid_pairs, 64 + 128 * G, kDv2SmemBytes, st_dv>>>(                   \
+            map_g, map_at, vt, rnorm_v, dv, n_rows, n_pairs, n_a_pad / kDvBK, C, P, reverse ? 1 : 0, gmax_bits);  \
     } while (0)
-            if (env.dv_groups == 4) { if (P == 196) AVT_DV(4, 196); else AVT_DV(4, 0); }
-            else { if (P == 196) AVT_DV(2, 196); else AVT_DV(2, 0); }
+#define AVT_DV_P(G, BM) do { if (P == 196) AVT_DV(G, 196, BM); else AVT_DV(G, 0, BM); } while (0)
+            if (env.dv_groups == 4) { if (b_mn) AVT_DV_P(4, true); else AVT_DV_P(4, false); }
+            else { if (b_mn) AVT_DV_P(2, true); else AVT_DV_P(2, false); }
+#undef AVT_DV_P
 #undef AVT_DV
         } else {
             const int grid = n_tiles < sms ? n_tiles : sms;
@@ -870,13 +915,17 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
         const int n_chunks = (n_rows + bk - 1) / bk;
         int splits = sms / n_mt;                 // one split per SM: fewer splits cut the atomics but lose
                                                  // more in streaming bandwidth (measured at 128..512 rows/rank)
+        if (cosched && dv_ctas > 0 && dv_ctas < sms) {      // the SMs the dv kernel leaves free
+            const int want = env.da_splits > 0 ? env.da_splits : (sms - dv_ctas) / n_mt;
+            if (want >= 1 && want < splits) splits = want;
+        }
         if (splits < 1) splits = 1;
         if (splits > n_chunks) splits = n_chunks;
         if (pair) {
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDa2SmemBytes));
-            bwd_da_pair_kernel<<<n_mt * splits, kDa2Threads, kDa2SmemBytes, st_da>>>(map_g, map_vt, d_ahat, N_a,
-                                                                                  n_mt, splits, n_chunks, C, gmax_bits);
+            bwd_da_pair_kernel<<<n_mt * splits, kDa2Threads, kDa2SmemBytes, st_da>>>(
+                map_g, map_vt, d_ahat, N_a, n_mt, splits, n_chunks, C, gmax_bits, (cosched ? 1 : 0) | (reverse ? 2 : 0));
         } else {
             AVT_CHECK_CUDA(cudaFuncSetAttribute(bwd_da_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)kDaSmemBytes));
