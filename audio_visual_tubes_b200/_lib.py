@@ -16,6 +16,7 @@ PRECISION_FP32 = 0
 PRECISION_F16 = 1
 GT_VGGSS, GT_FLICKR, GT_FLICKR_FRAME = 0, 1, 2
 EVAL_WORKSPACE_BYTES = 64
+MTC_STATIC_MAX_FRAMES = 4096
 DTYPE_F32, DTYPE_F16, DTYPE_BF16 = 0, 1, 2
 STAGE_PREP, STAGE_SIM, BWD_ROWGRAD_DONE = 1, 2, 1
 
@@ -47,6 +48,7 @@ SIGNATURES = {
     "avt_rasterise_gt": (_i, [_p, _p, _i, _i, _i, _p, _p]),
     "avt_auc": (_i, [_p, _i, _p, _p, _p]),
     "avt_mtc": (_i, [_p, _i, _p, _p, _p, _p]),
+    "avt_mtc_static": (_i, [_p, _i, _p, _p]),
     "avt_spectrogram_frames": (_i, [_i]),
     "avt_log_spectrogram": (_i, [_p, _p, _i, _ll, _i, _p, _d, _d, _d, _p, _i, _p]),
     "avt_log_spectrogram_pcm16": (_i, [_p, _p, _i, _ll, _i, _p, _d, _d, _d, _p, _i, _p]),

@@ -18,6 +18,7 @@
 // whose boundary is located by searching the float key space with the very same f.
 #include "avt_common.cuh"
 #include <atomic>
+#include <mutex>
 
 #ifndef AVT_EVAL_REGS
 #define AVT_EVAL_REGS 64
@@ -1048,6 +1049,56 @@ extern "C" int avt_mtc(const uint8_t* masks, int T, int32_t* pair_inter, int32_t
                        float* out, void* stream) {
     AVT_REQUIRE(masks && pair_inter && pair_union && out, "avt_mtc: null pointer");
     AVT_REQUIRE(T >= 2, "avt_mtc: T=%d needs at least two frames", T);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    mtc_pairs_kernel<<<T - 1, 256, 0, st>>>(masks, pair_inter, pair_union);
+    AVT_LAUNCH_CHECK();
+    mtc_mean_kernel<<<1, 32, 0, st>>>(pair_inter, pair_union, T, out);
+    AVT_LAUNCH_CHECK();
+    return AVT_OK;
+}
+
+// ---- avt_mtc without caller scratch (no counterpart in the reference; added
+// for callers that may not allocate: graph capture, serving loops).  The pair counts
+// live in a file-scope device array of fixed size -- every GPU that loads the library holds these
+// 32 KB until the process exits.  In HOST code `g_mtc_static_scratch` is only a stand-in for the
+// symbol, not a device address: the address is fetched once per device, with that device current,
+// by cudaGetSymbolAddress, and that pointer is what the kernels get.
+static __device__ __align__(256) int32_t g_mtc_static_scratch[2 * AVT_MTC_STATIC_MAX_FRAMES];
+
+namespace avt {
+constexpr int kMaxStaticDevices = 64;
+static int mtc_static_scratch(int32_t** out) {
+    static std::mutex mu;
+    static int32_t* addr[kMaxStaticDevices] = {};
+    int dev = 0;
+    AVT_CHECK_CUDA(cudaGetDevice(&dev));
+    AVT_REQUIRE(dev >= 0 && dev < kMaxStaticDevices, "avt_mtc_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        AVT_CHECK_CUDA(cudaGetSymbolAddress(&p, g_mtc_static_scratch));   // this device's copy of the array
+        AVT_REQUIRE(p != nullptr, "avt_mtc_static: cudaGetSymbolAddress returned a null address");
+        addr[dev] = static_cast<int32_t*>(p);
+    }
+    *out = addr[dev];
+    return AVT_OK;
+}
+}  // namespace avt
+
+extern "C" int avt_mtc_static(const uint8_t* masks, int T, float* out, void* stream) {
+    AVT_REQUIRE(masks && out, "avt_mtc_static: null pointer");
+    AVT_REQUIRE(T >= 2, "avt_mtc_static: T=%d needs at least two frames", T);
+    AVT_REQUIRE(T <= AVT_MTC_STATIC_MAX_FRAMES,
+                "avt_mtc_static: T=%d exceeds AVT_MTC_STATIC_MAX_FRAMES=%d (the built-in scratch holds no more; "
+                "use avt_mtc with caller scratch)", T, AVT_MTC_STATIC_MAX_FRAMES);
+    int32_t* scratch = nullptr;
+    int rc = mtc_static_scratch(&scratch);
+    if (rc != AVT_OK) return rc;
+    // Both halves are WRITTEN for every pair [0, T-1) by mtc_pairs_kernel before mtc_mean_kernel reads
+    // exactly those entries, so nothing has to start at zero and what an earlier call left behind is
+    // never read.  Calls that overlap on the GPU (two streams, two threads) share the array and race.
+    int32_t* pair_inter = scratch;
+    int32_t* pair_union = scratch + AVT_MTC_STATIC_MAX_FRAMES;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     mtc_pairs_kernel<<<T - 1, 256, 0, st>>>(masks, pair_inter, pair_union);
     AVT_LAUNCH_CHECK();

@@ -224,6 +224,18 @@ int avt_auc(const double* ciou, int N, int32_t* counts, double* out, void* strea
 int avt_mtc(const uint8_t* masks, int T, int32_t* pair_inter, int32_t* pair_union,
             float* out, void* stream);
 
+/* avt_mtc for callers that can not allocate (code under CUDA graph capture, serving loops, harnesses
+ * that forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * Same masks / T / out and the same result as avt_mtc, but the pair
+ * counts live in a fixed device array inside the library (2 x AVT_MTC_STATIC_MAX_FRAMES int32 = 32 KB,
+ * held by every GPU that loads the library until the process exits); the call allocates nothing.
+ * T > AVT_MTC_STATIC_MAX_FRAMES returns AVT_ERR_INVALID (use avt_mtc with caller scratch).  Every call
+ * on a device shares that array: calls whose kernels may overlap on the GPU (different streams or
+ * host threads) race with each other -- serialise them.  Nothing in the array has to be cleared between
+ * calls (each call writes every entry it later reads). */
+#define AVT_MTC_STATIC_MAX_FRAMES 4096
+int avt_mtc_static(const uint8_t* masks, int T, float* out, void* stream);
+
 /* The per-video metrics of the PerFrameLabels test loop, train_hardway.py:163-203: video v owns
  * frames [v*F, (v+1)*F) of ciou [V*F] float64 and masks [V*F,224,224] uint8 (both as
  * avt_eval_maps wrote them).  out [V,3] float64 (device):
