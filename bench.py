@@ -427,7 +427,13 @@ def main():
 
 # DRAM bytes per launch of the step's kernels from the committed `ncu --set full` capture of this same
 # command (dram__bytes_read.sum + dram__bytes_write.sum); filled from profiles/ by hand after each capture
-NCU_TRAFFIC = {}
+NCU_TRAFFIC = {
+    # profiles/r2_ncu_head.txt (B = 1024): dram__bytes_read.sum + dram__bytes_write.sum per launch
+    "sim": (206696192 + 12365312, "profiles/r2_ncu_head.txt"),
+    "bwd_g": (220016384 + 361715968, "profiles/r2_ncu_head.txt"),
+    "bwd_dv": (620157952 + 381518080, "profiles/r2_ncu_head.txt"),
+    "bwd_da": (618686464 + 4047104, "profiles/r2_ncu_head.txt"),
+}
 
 
 def e2e_leg(args, avt, cfg, hs, v, a, dev, world, barrier, loss_val, cells_per_step):
@@ -497,8 +503,21 @@ def e2e_leg(args, avt, cfg, hs, v, a, dev, world, barrier, loss_val, cells_per_s
            "path": "HostHeadPipeline.submit (double-buffered: H2D of step i+1 under compute of step i), "
                    + ("fp16 host features" if "f16_features" in out else "fp32 host features")
                    + "; dv stays on the device for the backbone's backward, the loss (4 B) is read back every step",
-           "variants": out, "serial_fp32_ms_per_step": t_serial * 1e3}
+           "variants": out, "serial_fp32_ms_per_step": t_serial * 1e3, "pcie": pcie_link(dev)}
     return e2e
+
+
+def pcie_link(dev):
+    """Generation and width the GPU's PCIe link is running at: the e2e leg is the H2D copy, so a box
+    whose link trained at half rate (seen in this pool: 28.6 instead of 54 GB/s) halves it."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(dev.index or 0)
+        return {"gen": pynvml.nvmlDeviceGetCurrPcieLinkGeneration(h), "width": pynvml.nvmlDeviceGetCurrPcieLinkWidth(h),
+                "gen_max": pynvml.nvmlDeviceGetMaxPcieLinkGeneration(h), "width_max": pynvml.nvmlDeviceGetMaxPcieLinkWidth(h)}
+    except Exception as e:                                   # noqa: BLE001
+        return {"error": repr(e)[:120]}
 
 
 # ----------------------------------------------------------------------------- CPU eval baseline
@@ -663,7 +682,7 @@ def extras(avt, ev, _lib, cfg, dev, pk):
     out["eval_cfg3"] = {"maps_per_s": n / (ms * 1e-3), "ms": ms, "mode": "materialising (dense GT, up224 + mask out)",
                         "roofline": {"kernel": "eval_maps_kernel<true>", "bound": "hbm", "achieved": gbs,
                                      "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
-                                     "traffic": 289898496 + 1245011000, "traffic_source": "profiles/r1_ncu_eval_final.txt"}}
+                                     "traffic": 293586432 + 1246250000, "traffic_source": "profiles/r2_ncu_eval.txt"}}
     ms2 = timed(lambda: run_eval(False), 10, 3)
     out["eval_cfg3_metrics_only"] = {"maps_per_s": n / (ms2 * 1e-3), "ms": ms2}
     # the pipeline mode of the reference's test loop: boxes in (utils.py:264-273 rasterised inside
