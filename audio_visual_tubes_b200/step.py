@@ -89,7 +89,12 @@ class HeadStep:
             self.side.wait_stream(main)
             with torch.cuda.stream(self.side):
                 dist.all_reduce(total, group=self.group)
-        ext = self.dv_stream if (self.sharded and self.overlap) else None
+        # only the tensor-core backward has a separate dv contraction to move; forking the stream here keeps
+        # it inside a capture even if the library leaves it unused (joining an un-forked stream under
+        # capture is cudaErrorStreamCaptureIsolation)
+        ext = self.dv_stream if (self.sharded and self.overlap and cfg.precision == "f16") else None
+        if ext is not None:
+            ext.wait_stream(main)
         dv, d_ahat = head_backward_raw(v, a_hat, cfg, out, 0.0, None, None, col_offset, rowgrad_done=True,
                                        dv_stream=ext)
         if self.sharded:

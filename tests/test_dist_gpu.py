@@ -84,6 +84,9 @@ def _worker(rank, world, port, b_global, precision, out_dir):
             res["oracle_loss"] = float(o["loss"])
             res["oracle_dv"] = float(np.linalg.norm(dv1.cpu().numpy() - dv_o) / np.linalg.norm(dv_o))
             res["oracle_da"] = float(np.linalg.norm(da1.cpu().numpy() - da_o) / np.linalg.norm(da_o))
+            # the sharded result held to the oracle by itself, on this rank's rows
+            res["oracle_da_sharded"] = float(np.linalg.norm(da_g.cpu().numpy() - da_o[sl]) / np.linalg.norm(da_o[sl]))
+            res["oracle_dv_sharded"] = float(np.linalg.norm(dv_g.cpu().numpy() - dv_o[sl]) / np.linalg.norm(dv_o[sl]))
         np.save(os.path.join(out_dir, f"r{rank}.npy"), res, allow_pickle=True)
         mark("results saved")
         dist.barrier()
@@ -126,7 +129,16 @@ def _run(world, b_global, precision, tmp_path, limit_s=300):
         # the fp16 cell gradients (max over the rank's rows vs over all rows) and the order of the
         # d_ahat atomics / reduce_scatter differ
         assert z["dv_e"] < 1e-5 and z["dv_g"] < 1e-5, (r, z)
-        assert z["da_e"] < 1e-5 and z["da_g"] < 1e-5, (r, z)
+        # d_ahat sums over ALL visual rows in fp32 inside tensor memory.  One GPU runs the K = N_v*196 rows as
+        # a few long accumulation chains (7 K splits beside the dv kernel), a rank of `world` runs 1/world of
+        # them and the partial sums meet in the reduce_scatter: same terms, different association.  At
+        # B = 256 / world 2 the chains are short and the two agree to 1e-5; at B = 1024 / world 8 the single-GPU
+        # chains are 8x longer (1792 accumulations each) and the two differ by ~1e-4 while each sits 1.5e-4
+        # from the fp64 oracle (measured: profiles/r2_pytest_dist_gpu.txt) -- the 2e-3 contract is checked
+        # against the oracle below for BOTH.  A mis-scattered or dropped block would be >= 3e-4 coherent and
+        # would also break the loss / dv equalities above.
+        da_tol = 1e-5 if b_global <= 256 else 3e-4
+        assert z["da_e"] < da_tol and z["da_g"] < da_tol, (r, z)
         if precision == "f16":     # (the fp32 CUDA-core path accumulates dv with atomics)
             assert z["dv_bits"], "graph replay and eager sharded step disagree on dv"
         assert z["logits_bits"] and z["A_bits"], (r, z)
@@ -134,6 +146,7 @@ def _run(world, b_global, precision, tmp_path, limit_s=300):
     gtol = 2e-3 if precision == "f16" else 2e-4
     assert abs(z["loss1"] - z["oracle_loss"]) < 2e-3 * max(1.0, abs(z["oracle_loss"]))
     assert z["oracle_dv"] < gtol and z["oracle_da"] < gtol, z
+    assert z["oracle_dv_sharded"] < gtol and z["oracle_da_sharded"] < gtol, z
 
 
 @pytest.mark.timeout(600)
