@@ -982,6 +982,17 @@ def extras_collective(avt, ev, _lib, cfg, dev, world, rank, barrier):
     torch.manual_seed(0)
     net = avt.AVENet(args, False, precision=cfg.precision).to(dev).train()
     model = net
+    # the stock ResNets keep their `fc` layers for checkpoint compatibility; nothing on this path uses
+    # them (in the reference they simply never get a gradient) and DDP must not wait for theirs
+    # (nor the stems of the other modality: conv1_a / conv1_flow / audnet.conv1).  One small probe backward
+    # finds them: whatever gets no gradient from the features is frozen.
+    f_i, f_a = net.features(torch.randn(2, 3, 224, 224, device=dev), torch.randn(2, 1, 257, 300, device=dev))
+    (f_i.float().sum() + f_a.float().sum()).backward()
+    for _, prm in net.named_parameters():
+        if prm.grad is None:
+            prm.requires_grad_(False)
+    net.zero_grad(set_to_none=True)
+    del f_i, f_a
     if world > 1:
         from torch.nn.parallel import DistributedDataParallel as DDP
 
@@ -992,7 +1003,7 @@ def extras_collective(avt, ev, _lib, cfg, dev, world, rank, barrier):
             def forward(self, image, audio):
                 return self.n.features(image, audio)
         model = DDP(_Features(net), device_ids=[dev.index])
-    opt = torch.optim.Adam(net.parameters(), lr=1e-6, weight_decay=1e-4)
+    opt = torch.optim.Adam([q for q in net.parameters() if q.requires_grad], lr=1e-6, weight_decay=1e-4)
     g = torch.Generator(device=dev).manual_seed(100 + rank)
     img = torch.randn(128, 3, 224, 224, device=dev, generator=g)
     spec = torch.randn(128, 1, 257, 300, device=dev, generator=g)
