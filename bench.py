@@ -1008,6 +1008,18 @@ def extras_collective(avt, ev, _lib, cfg, dev, world, rank, barrier):
     img = torch.randn(128, 3, 224, 224, device=dev, generator=g)
     spec = torch.randn(128, 1, 257, 300, device=dev, generator=g)
     for tag, amp in (("fp32_backbones", False), ("bf16_autocast_backbones", True)):
+        if amp:
+            # stock PyTorch's fast path for convolutions under autocast: NHWC weights and inputs
+            try:
+                net = net.to(memory_format=torch.channels_last)
+                img = img.contiguous(memory_format=torch.channels_last)
+                spec = spec.contiguous(memory_format=torch.channels_last)
+                if world > 1:
+                    model = DDP(_Features(net), device_ids=[dev.index])
+            except Exception as e:                           # noqa: BLE001
+                out[f"train_cfg2_b128_per_gpu_{tag}"] = {"error": repr(e)[:300]}
+                continue
+
         def train_step():
             opt.zero_grad(set_to_none=True)
             with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
@@ -1026,7 +1038,7 @@ def extras_collective(avt, ev, _lib, cfg, dev, world, rank, barrier):
             out[f"train_cfg2_b128_per_gpu_{tag}"] = {
                 "clips_per_s": world * 128 / (ms * 1e-3), "ms_per_step": ms, "n_gpus": world,
                 "global_batch": world * 128,
-                "note": "stock PyTorch ResNet-18 backbones" + (" under bf16 autocast (features reach the head as bf16)" if amp else " in fp32 (as the reference runs them)")
+                "note": "stock PyTorch ResNet-18 backbones" + (" under bf16 autocast + channels_last (features reach the head as bf16)" if amp else " in fp32 (as the reference runs them)")
                         + (", DDP gradient all-reduce; head row-sharded with global negatives" if world > 1 else "; head = libavtubes")
                         + "; Adam(lr 1e-6, wd 1e-4)"}
         except Exception as e:                               # noqa: BLE001
