@@ -869,7 +869,13 @@ int launch_bwd_f16(const float* v, const __half* vt, const __half* a_h,
             const int n_pairs = (n_tiles + 1) / 2;
             int grid_pairs = n_pairs < sms / 2 ? n_pairs : sms / 2;
             if (cosched) {
-                const int want = env.dv_pairs > 0 ? env.dv_pairs : (sms / 2) * 5 / 8;
+                // dv's share of the SM pairs: its store-bound epilogue costs the same per row whatever N_a is,
+                // the d_ahat contraction shrinks with N_a -- 5/8 at >= 1024 audio rows, 2/3 at 512, 3/4 below
+                // (profiles/r2_ab_cosched_small.txt: backward 63.6 -> 52.3 us at B = 128, 114.8 -> 101.3 at 256)
+                const int slots = sms / 2;
+                const int share = n_a_pad >= 1024 ? (slots * 5 + 4) / 8 : n_a_pad >= 512 ? (slots * 2 + 1) / 3
+                                                                                       : (slots * 3 + 2) / 4;
+                const int want = env.dv_pairs > 0 ? env.dv_pairs : share;
                 if (want >= 1 && want < grid_pairs) grid_pairs = want;
             }
             dv_ctas = 2 * grid_pairs;
