@@ -33,6 +33,21 @@ def test_library_exports_every_declared_symbol(lib):
     assert sorted(_lib.SIGNATURES) == names, "ctypes prototypes out of sync with the header"
 
 
+def test_header_constants_match_the_binding():
+    from audio_visual_tubes_b200 import _lib
+    src = open(os.path.join(ROOT, "include", "avtubes.h")).read()
+    consts = {k: int(v) for k, v in re.findall(r"#define\s+(AVT_[A-Z0-9_]+)\s+(-?\d+)\b", src)}
+    assert consts["AVT_MTC_STATIC_MAX_FRAMES"] == _lib.MTC_STATIC_MAX_FRAMES
+    assert consts["AVT_EVAL_WORKSPACE_BYTES"] == _lib.EVAL_WORKSPACE_BYTES
+    assert (consts["AVT_PRECISION_FP32"], consts["AVT_PRECISION_F16"]) == (_lib.PRECISION_FP32, _lib.PRECISION_F16)
+    assert (consts["AVT_DTYPE_F32"], consts["AVT_DTYPE_F16"], consts["AVT_DTYPE_BF16"]) == \
+        (_lib.DTYPE_F32, _lib.DTYPE_F16, _lib.DTYPE_BF16)
+    assert (consts["AVT_STAGE_PREP"], consts["AVT_STAGE_SIM"], consts["AVT_BWD_ROWGRAD_DONE"]) == \
+        (_lib.STAGE_PREP, _lib.STAGE_SIM, _lib.BWD_ROWGRAD_DONE)
+    assert (consts["AVT_GT_VGGSS"], consts["AVT_GT_FLICKR"], consts["AVT_GT_FLICKR_FRAME"]) == \
+        (_lib.GT_VGGSS, _lib.GT_FLICKR, _lib.GT_FLICKR_FRAME)
+
+
 def test_version_and_error_paths_without_gpu(lib):
     assert lib.avt_version() >= 100
     # argument validation happens before any CUDA call: bad shapes report AVT_ERR_INVALID
