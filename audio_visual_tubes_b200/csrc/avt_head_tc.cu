@@ -115,8 +115,19 @@ __device__ __forceinline__ void cell_chunk(const uint32_t (&r)[N], const CellCtx
             const float2 f = ffma2(fadd2(s, splat(-cx.sm)), u, splat(1.0f));
             const float2 gv = fmul2(fmul2(w, splat(cx.coef)), f);
             const __half2 h = __floats2half2_rn(gv.x, gv.y);
+#ifndef AVT_G_SCALAR_ST
+            // Lanes 2j / 2j+1 hold audio columns k, k+1 of the same two positions: they swap halves so
+            // that the even lane stores (k, k+1) of position i and the odd lane (k, k+1) of position i+1
+            // as ONE 4-byte word each -- half the store instructions (the epilogue sits in LG throttle
+            // 10 % of the time: profiles/r2_ncu_head.txt).  `gp` was moved to this lane's word by the caller.
+            const uint32_t mine = *reinterpret_cast<const uint32_t*>(&h);
+            const uint32_t other = __shfl_xor_sync(0xffffffffu, mine, 1);
+            const uint32_t word = (threadIdx.x & 1u) ? __byte_perm(other, mine, 0x7632) : __byte_perm(mine, other, 0x5410);
+            *reinterpret_cast<uint32_t*>(gp + (uint32_t)i * pitch) = word;
+#else
             gp[(uint32_t)i * pitch] = __low2half(h);
             gp[(uint32_t)(i + 1) * pitch] = __high2half(h);
+#endif
         } else {
             dn = fadd2(dn, w);
             num = ffma2(w, s, num);
@@ -347,7 +358,12 @@ sim_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
                     exact = __any_sync(0xffffffffu, dnk < kTinyDen);
                     fetch(n + groups);
                 }
+#ifndef AVT_G_SCALAR_ST
+                // this lane's 4-byte word: columns (k, k+1) of position i (even lane) or (k-1, k) of i+1 (odd)
+                __half* gout = G + (size_t)n * P * n_a_pad + k + ((lane & 1) ? (int)n_a_pad - 1 : 0);
+#else
                 __half* gout = G + (size_t)n * P * n_a_pad + k;
+#endif
                 const uint32_t pitch = (uint32_t)n_a_pad;
                 AVT_TRACE(e0 = clock64();)
                 mbar_wait(&tmem_full[buf], use & 1u);
